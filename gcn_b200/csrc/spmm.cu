@@ -1,0 +1,401 @@
+// Host side of the SpMM engine: plan construction (CSR upload, row classes, transpose), kernel
+// dispatch by feature width / dtype / alignment, the host-buffer end-to-end entry point.
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "common.h"
+#include "spmm_kernels.cuh"
+
+namespace gcnb {
+
+struct Matrix {  // one CSR resident in HBM + its block-class work lists
+  int64_t m = 0, n = 0, nnz = 0;
+  int32_t* rowptr = nullptr;      // [m+1]
+  int2* cv = nullptr;             // [nnz+2] interleaved (col, val-bits)
+  WorkItem* items = nullptr;      // [n_items]
+  int32_t* split_rows = nullptr;  // [n_split] rows cut into >1 item
+  int32_t* split_ptr = nullptr;   // [n_split+1] first partial slot of each split row
+  int64_t n_items = 0, n_split = 0, n_partials = 0, n_long_rows = 0, max_row_nnz = 0;
+  size_t bytes = 0;
+
+  void release() {
+    cudaFree(rowptr); cudaFree(cv); cudaFree(items); cudaFree(split_rows); cudaFree(split_ptr);
+    rowptr = nullptr; cv = nullptr; items = nullptr; split_rows = nullptr; split_ptr = nullptr;
+  }
+};
+
+}  // namespace gcnb
+
+struct gcnb_plan {
+  int device = 0;
+  int n_sm = 0;
+  bool symmetric = false;
+  bool has_t = false;
+  gcnb::Matrix a, at;
+  // staging for gcnb_spmm_host (grown on demand; that entry point is not re-entrant per plan)
+  float* stage_b = nullptr;
+  float* stage_c = nullptr;
+  size_t stage_b_bytes = 0, stage_c_bytes = 0;
+};
+
+namespace gcnb {
+
+static int upload_matrix(const int32_t* rowptr, const int32_t* col, const float* val, int64_t m,
+                         int64_t n, int64_t nnz, Matrix* M) {
+  M->m = m; M->n = n; M->nnz = nnz;
+  // block-class work lists (host, O(m))
+  std::vector<WorkItem> items;
+  std::vector<int32_t> split_rows, split_ptr;
+  int64_t n_partials = 0, max_len = 0, n_long = 0;
+  for (int64_t r = 0; r < m; ++r) {
+    const int64_t beg = rowptr[r], end = rowptr[r + 1];
+    const int64_t len = end - beg;
+    max_len = std::max(max_len, len);
+    if (len < kLongRow) continue;
+    ++n_long;
+    if (len <= kChunk) {
+      items.push_back({(int32_t)r, (int32_t)beg, (int32_t)end, -1});
+    } else {
+      // equal-sized pieces, each <= kChunk
+      const int64_t pieces = (len + kChunk - 1) / kChunk;
+      const int64_t per = (len + pieces - 1) / pieces;
+      split_rows.push_back((int32_t)r);
+      split_ptr.push_back((int32_t)n_partials);
+      for (int64_t b = beg; b < end; b += per)
+        items.push_back({(int32_t)r, (int32_t)b, (int32_t)std::min(end, b + per),
+                         (int32_t)n_partials++});
+    }
+  }
+  split_ptr.push_back((int32_t)n_partials);
+  M->n_items = (int64_t)items.size();
+  M->n_split = (int64_t)split_rows.size();
+  M->n_partials = n_partials;
+  M->n_long_rows = n_long;
+  M->max_row_nnz = max_len;
+
+  GCNB_CHECK_CUDA(cudaMalloc(&M->rowptr, (size_t)(m + 1) * sizeof(int32_t)));
+  GCNB_CHECK_CUDA(cudaMalloc(&M->cv, (size_t)(nnz + 2) * sizeof(int2)));
+  M->bytes = (size_t)(m + 1) * 4 + (size_t)(nnz + 2) * 8;
+  GCNB_CHECK_CUDA(cudaMemcpy(M->rowptr, rowptr, (size_t)(m + 1) * sizeof(int32_t),
+                             cudaMemcpyHostToDevice));
+  GCNB_CHECK_CUDA(cudaMemset(M->cv + nnz, 0, 2 * sizeof(int2)));
+  if (nnz > 0) {
+    int32_t* d_col = nullptr;
+    float* d_val = nullptr;
+    GCNB_CHECK_CUDA(cudaMalloc(&d_col, (size_t)nnz * 4));
+    GCNB_CHECK_CUDA(cudaMalloc(&d_val, (size_t)nnz * 4));
+    GCNB_CHECK_CUDA(cudaMemcpy(d_col, col, (size_t)nnz * 4, cudaMemcpyHostToDevice));
+    GCNB_CHECK_CUDA(cudaMemcpy(d_val, val, (size_t)nnz * 4, cudaMemcpyHostToDevice));
+    const int64_t blocks = (nnz + 255) / 256;
+    interleave_kernel<<<(unsigned)blocks, 256>>>(d_col, d_val, M->cv, nnz);
+    GCNB_CHECK_CUDA(cudaGetLastError());
+    GCNB_CHECK_CUDA(cudaDeviceSynchronize());
+    cudaFree(d_col);
+    cudaFree(d_val);
+  }
+  if (!items.empty()) {
+    GCNB_CHECK_CUDA(cudaMalloc(&M->items, items.size() * sizeof(WorkItem)));
+    GCNB_CHECK_CUDA(cudaMemcpy(M->items, items.data(), items.size() * sizeof(WorkItem),
+                               cudaMemcpyHostToDevice));
+    M->bytes += items.size() * sizeof(WorkItem);
+  }
+  if (!split_rows.empty()) {
+    GCNB_CHECK_CUDA(cudaMalloc(&M->split_rows, split_rows.size() * 4));
+    GCNB_CHECK_CUDA(cudaMalloc(&M->split_ptr, split_ptr.size() * 4));
+    GCNB_CHECK_CUDA(cudaMemcpy(M->split_rows, split_rows.data(), split_rows.size() * 4,
+                               cudaMemcpyHostToDevice));
+    GCNB_CHECK_CUDA(cudaMemcpy(M->split_ptr, split_ptr.data(), split_ptr.size() * 4,
+                               cudaMemcpyHostToDevice));
+    M->bytes += (split_rows.size() + split_ptr.size()) * 4;
+  }
+  return GCNB_OK;
+}
+
+// CSR transpose by counting sort: columns of every output row come out ascending.
+static void transpose_csr(const int32_t* rowptr, const int32_t* col, const float* val, int64_t m,
+                          int64_t n, int64_t nnz, std::vector<int32_t>& t_rowptr,
+                          std::vector<int32_t>& t_col, std::vector<float>& t_val) {
+  t_rowptr.assign((size_t)n + 1, 0);
+  t_col.resize((size_t)nnz);
+  t_val.resize((size_t)nnz);
+  for (int64_t z = 0; z < nnz; ++z) ++t_rowptr[(size_t)col[z] + 1];
+  for (int64_t c = 0; c < n; ++c) t_rowptr[c + 1] += t_rowptr[c];
+  std::vector<int32_t> cursor(t_rowptr.begin(), t_rowptr.end() - 1);
+  for (int64_t r = 0; r < m; ++r)
+    for (int64_t z = rowptr[r]; z < rowptr[r + 1]; ++z) {
+      const int32_t p = cursor[col[z]]++;
+      t_col[p] = (int32_t)r;
+      t_val[p] = val[z];
+    }
+}
+
+// ---- dispatch ------------------------------------------------------------------------------------
+struct LaunchArgs {
+  const Matrix* M;
+  const void* B;
+  int64_t ldb;
+  float* C;
+  int64_t ldc;
+  int k;
+  const float* bias;
+  int epi;
+  float* partials;
+  cudaStream_t stream;
+};
+
+template <typename TB, int VEC, int G, int NV>
+static int launch_one(const LaunchArgs& a) {
+  const Matrix& M = *a.M;
+  const int W = G * NV * VEC;
+  const unsigned ytiles = (unsigned)((a.k + W - 1) / W);
+  const int rows_per_cta = kRowWarps * (32 / G);
+  const int64_t gx = (M.m + rows_per_cta - 1) / rows_per_cta;
+  if (gx > 0x7fffffffLL) return set_error(GCNB_ERR_UNSUPPORTED, "too many rows for one grid");
+  const int long_thresh = M.n_items > 0 ? kLongRow : 0x7fffffff;
+  if (gx > 0) {
+    spmm_rows_kernel<TB, VEC, G, NV><<<dim3((unsigned)gx, ytiles), kRowWarps * 32, 0, a.stream>>>(
+        M.rowptr, M.cv, (const TB*)a.B, a.ldb, a.C, a.ldc, M.m, a.k, a.bias, a.epi, long_thresh);
+    GCNB_CHECK_CUDA(cudaGetLastError());
+  }
+  if (M.n_items > 0) {
+    spmm_block_kernel<TB, VEC, G, NV>
+        <<<dim3((unsigned)M.n_items, ytiles), kBlockWarps * 32, 0, a.stream>>>(
+            M.items, M.cv, (const TB*)a.B, a.ldb, a.C, a.ldc, a.partials, a.k, a.bias, a.epi);
+    GCNB_CHECK_CUDA(cudaGetLastError());
+    if (M.n_split > 0) {
+      spmm_reduce_kernel<<<(unsigned)M.n_split, 128, 0, a.stream>>>(
+          M.split_rows, M.split_ptr, a.partials, a.C, a.ldc, a.k, a.bias, a.epi);
+      GCNB_CHECK_CUDA(cudaGetLastError());
+    }
+  }
+  return GCNB_OK;
+}
+
+template <typename TB, int VEC, int NVMAX>
+static int launch_vec(const LaunchArgs& a) {
+  const int nvec = (a.k + VEC - 1) / VEC;  // vectors per feature row
+  if (nvec <= 4) return launch_one<TB, VEC, 4, 1>(a);
+  if (nvec <= 8) return launch_one<TB, VEC, 8, 1>(a);
+  if (nvec <= 16) return launch_one<TB, VEC, 16, 1>(a);
+  if (nvec <= 32) return launch_one<TB, VEC, 32, 1>(a);
+  // wide rows: whole warp per row, NV vectors per lane, as few column tiles as possible
+  const int tiles = (nvec + 32 * NVMAX - 1) / (32 * NVMAX);
+  const int nv = (nvec + 32 * tiles - 1) / (32 * tiles);
+  if (nv <= 1) return launch_one<TB, VEC, 32, 1>(a);
+  if (nv == 2) return launch_one<TB, VEC, 32, 2>(a);
+  if constexpr (NVMAX >= 4) {
+    if (nv == 3) return launch_one<TB, VEC, 32, 3>(a);
+    return launch_one<TB, VEC, 32, 4>(a);
+  } else {
+    return launch_one<TB, VEC, 32, 2>(a);
+  }
+}
+
+static inline bool aligned(const void* p, size_t a) { return ((uintptr_t)p % a) == 0; }
+
+static int spmm_dispatch(const Matrix& M, const void* B, int b_dtype, int64_t ldb, float* C,
+                         int64_t ldc, int k, const float* bias, int epi, cudaStream_t stream) {
+  if (M.m == 0 || k == 0) return GCNB_OK;
+  float* partials = nullptr;
+  if (M.n_partials > 0)
+    GCNB_CHECK_CUDA(cudaMallocAsync(&partials, (size_t)M.n_partials * k * sizeof(float), stream));
+  LaunchArgs a{&M, B, ldb, C, ldc, k, bias, epi, partials, stream};
+  int rc;
+  // vector width: limited by k, both leading dimensions and base alignment (C is stored with
+  // min(VEC,4) floats per store)
+  if (b_dtype == GCNB_F32) {
+    if (k % 4 == 0 && ldb % 4 == 0 && ldc % 4 == 0 && aligned(B, 16) && aligned(C, 16))
+      rc = launch_vec<float, 4, 4>(a);
+    else if (k % 2 == 0 && ldb % 2 == 0 && ldc % 2 == 0 && aligned(B, 8) && aligned(C, 8))
+      rc = launch_vec<float, 2, 4>(a);
+    else
+      rc = launch_vec<float, 1, 4>(a);
+  } else {
+    if (k % 8 == 0 && ldb % 8 == 0 && ldc % 4 == 0 && aligned(B, 16) && aligned(C, 16))
+      rc = launch_vec<__nv_bfloat16, 8, 2>(a);
+    else if (k % 4 == 0 && ldb % 4 == 0 && ldc % 4 == 0 && aligned(B, 8) && aligned(C, 16))
+      rc = launch_vec<__nv_bfloat16, 4, 4>(a);
+    else if (k % 2 == 0 && ldb % 2 == 0 && ldc % 2 == 0 && aligned(B, 4) && aligned(C, 8))
+      rc = launch_vec<__nv_bfloat16, 2, 4>(a);
+    else
+      rc = launch_vec<__nv_bfloat16, 1, 4>(a);
+  }
+  if (partials) cudaFreeAsync(partials, stream);
+  return rc;
+}
+
+static int check_operands(const gcnb_plan_t* plan, const void* B, int b_dtype, int64_t ldb,
+                          const float* C, int64_t ldc, int k, const float* bias, int epi) {
+  GCNB_REQUIRE(plan != nullptr, "plan is null");
+  GCNB_REQUIRE(k >= 0, "k = %d is negative", k);
+  GCNB_REQUIRE(b_dtype == GCNB_F32 || b_dtype == GCNB_BF16, "unknown b_dtype %d", b_dtype);
+  GCNB_REQUIRE(ldb >= k && ldc >= k, "leading dimensions (%lld, %lld) smaller than k = %d",
+               (long long)ldb, (long long)ldc, k);
+  GCNB_REQUIRE(k == 0 || (B != nullptr && C != nullptr), "B or C is null");
+  GCNB_REQUIRE(!(epi & GCNB_EPI_BIAS) || bias != nullptr, "GCNB_EPI_BIAS without a bias pointer");
+  GCNB_REQUIRE((epi & ~(GCNB_EPI_BIAS | GCNB_EPI_RELU)) == 0, "unknown epilogue flags %d", epi);
+  return GCNB_OK;
+}
+
+}  // namespace gcnb
+
+using namespace gcnb;
+
+extern "C" {
+
+int gcnb_plan_create(const int32_t* rowptr, const int32_t* col, const float* val, int64_t m,
+                     int64_t n, int64_t nnz, int flags, int device, gcnb_plan_t** plan_out) {
+  GCNB_REQUIRE(plan_out != nullptr, "plan_out is null");
+  *plan_out = nullptr;
+  GCNB_REQUIRE(m >= 0 && n >= 0 && nnz >= 0, "negative size (m=%lld n=%lld nnz=%lld)",
+               (long long)m, (long long)n, (long long)nnz);
+  GCNB_REQUIRE(rowptr != nullptr, "rowptr is null");
+  GCNB_REQUIRE(nnz == 0 || (col != nullptr && val != nullptr), "col or val is null");
+  GCNB_REQUIRE(m < 0x7fffffffLL && n < 0x7fffffffLL && nnz < 0x7ffffff0LL,
+               "int32 CSR limits exceeded (m=%lld n=%lld nnz=%lld)", (long long)m, (long long)n,
+               (long long)nnz);
+  GCNB_REQUIRE(rowptr[0] == 0 && rowptr[m] == nnz, "rowptr[0]=%d rowptr[m]=%d, expected 0 and %lld",
+               rowptr[0], rowptr[m], (long long)nnz);
+  for (int64_t r = 0; r < m; ++r) {
+    GCNB_REQUIRE(rowptr[r + 1] >= rowptr[r], "rowptr decreases at row %lld", (long long)r);
+    for (int64_t z = rowptr[r]; z < rowptr[r + 1]; ++z) {
+      GCNB_REQUIRE(col[z] >= 0 && col[z] < n, "column %d out of range at nz %lld", col[z],
+                   (long long)z);
+      GCNB_REQUIRE(z == rowptr[r] || col[z] > col[z - 1],
+                   "columns of row %lld are not strictly ascending", (long long)r);
+    }
+  }
+  int rc = require_gpu();
+  if (rc != GCNB_OK) return rc;
+  int ndev = gcnb_device_count();
+  GCNB_REQUIRE(device >= 0 && device < ndev, "device %d out of range (%d visible)", device, ndev);
+  DeviceGuard guard(device);
+  GCNB_CHECK_CUDA(guard.status);
+
+  gcnb_plan* p = new (std::nothrow) gcnb_plan();
+  if (!p) return set_error(GCNB_ERR_ALLOC, "out of host memory");
+  p->device = device;
+  p->n_sm = sm_count(device);
+  rc = upload_matrix(rowptr, col, val, m, n, nnz, &p->a);
+  if (rc != GCNB_OK) { gcnb_plan_destroy(p); return rc; }
+
+  if (flags & GCNB_PLAN_ASSUME_SYMMETRIC) {
+    if (m != n) { gcnb_plan_destroy(p); return set_error(GCNB_ERR_ARG, "ASSUME_SYMMETRIC with m != n"); }
+    p->symmetric = true;
+  } else if (!(flags & GCNB_PLAN_NO_TRANSPOSE)) {
+    std::vector<int32_t> t_rowptr, t_col;
+    std::vector<float> t_val;
+    transpose_csr(rowptr, col, val, m, n, nnz, t_rowptr, t_col, t_val);
+    if (m == n && memcmp(t_rowptr.data(), rowptr, (size_t)(m + 1) * 4) == 0 &&
+        (nnz == 0 || (memcmp(t_col.data(), col, (size_t)nnz * 4) == 0 &&
+                      memcmp(t_val.data(), val, (size_t)nnz * 4) == 0))) {
+      p->symmetric = true;  // bit-identical transpose: A^T·dY can run on A
+    } else {
+      rc = upload_matrix(t_rowptr.data(), t_col.data(), t_val.data(), n, m, nnz, &p->at);
+      if (rc != GCNB_OK) { gcnb_plan_destroy(p); return rc; }
+      p->has_t = true;
+    }
+  }
+  *plan_out = p;
+  return GCNB_OK;
+}
+
+int gcnb_plan_destroy(gcnb_plan_t* plan) {
+  if (!plan) return GCNB_OK;
+  DeviceGuard guard(plan->device);
+  plan->a.release();
+  plan->at.release();
+  cudaFree(plan->stage_b);
+  cudaFree(plan->stage_c);
+  delete plan;
+  return GCNB_OK;
+}
+
+int gcnb_plan_info(const gcnb_plan_t* plan, int64_t info[16]) {
+  GCNB_REQUIRE(plan != nullptr && info != nullptr, "null argument");
+  for (int i = 0; i < 16; ++i) info[i] = 0;
+  info[0] = plan->a.m; info[1] = plan->a.n; info[2] = plan->a.nnz;
+  info[3] = plan->symmetric; info[4] = plan->has_t;
+  info[5] = plan->a.m - plan->a.n_long_rows; info[6] = plan->a.n_long_rows;
+  info[7] = plan->a.n_items; info[8] = plan->a.max_row_nnz;
+  info[9] = (int64_t)(plan->a.bytes + plan->at.bytes + plan->stage_b_bytes + plan->stage_c_bytes);
+  info[10] = plan->n_sm; info[11] = plan->a.n_split;
+  return GCNB_OK;
+}
+
+int gcnb_spmm(const gcnb_plan_t* plan, const void* B, int b_dtype, int64_t ldb, float* C,
+              int64_t ldc, int k, const float* bias, int epilogue, void* stream) {
+  int rc = check_operands(plan, B, b_dtype, ldb, C, ldc, k, bias, epilogue);
+  if (rc != GCNB_OK) return rc;
+  DeviceGuard guard(plan->device);
+  GCNB_CHECK_CUDA(guard.status);
+  return spmm_dispatch(plan->a, B, b_dtype, ldb, C, ldc, k, bias, epilogue, (cudaStream_t)stream);
+}
+
+int gcnb_spmm_t(const gcnb_plan_t* plan, const void* B, int b_dtype, int64_t ldb, float* C,
+                int64_t ldc, int k, void* stream) {
+  int rc = check_operands(plan, B, b_dtype, ldb, C, ldc, k, nullptr, 0);
+  if (rc != GCNB_OK) return rc;
+  if (!plan->symmetric && !plan->has_t)
+    return set_error(GCNB_ERR_ARG, "plan was created with GCNB_PLAN_NO_TRANSPOSE");
+  DeviceGuard guard(plan->device);
+  GCNB_CHECK_CUDA(guard.status);
+  const Matrix& M = plan->symmetric ? plan->a : plan->at;
+  return spmm_dispatch(M, B, b_dtype, ldb, C, ldc, k, nullptr, 0, (cudaStream_t)stream);
+}
+
+int gcnb_spmm_host(gcnb_plan_t* plan, const float* B_host, float* C_host, int k, int transpose,
+                   void* stream) {
+  GCNB_REQUIRE(plan != nullptr, "plan is null");
+  GCNB_REQUIRE(k >= 0, "k = %d is negative", k);
+  GCNB_REQUIRE(k == 0 || (B_host && C_host), "host buffer is null");
+  if (transpose && !plan->symmetric && !plan->has_t)
+    return set_error(GCNB_ERR_ARG, "plan was created with GCNB_PLAN_NO_TRANSPOSE");
+  DeviceGuard guard(plan->device);
+  GCNB_CHECK_CUDA(guard.status);
+  const Matrix& M = (transpose && !plan->symmetric) ? plan->at : plan->a;
+  if (k == 0 || M.m == 0) return GCNB_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t bb = (size_t)M.n * k * sizeof(float), cb = (size_t)M.m * k * sizeof(float);
+  if (bb > plan->stage_b_bytes) {
+    cudaFree(plan->stage_b);
+    plan->stage_b = nullptr; plan->stage_b_bytes = 0;
+    GCNB_CHECK_CUDA(cudaMalloc(&plan->stage_b, bb));
+    plan->stage_b_bytes = bb;
+  }
+  if (cb > plan->stage_c_bytes) {
+    cudaFree(plan->stage_c);
+    plan->stage_c = nullptr; plan->stage_c_bytes = 0;
+    GCNB_CHECK_CUDA(cudaMalloc(&plan->stage_c, cb));
+    plan->stage_c_bytes = cb;
+  }
+  if (bb) GCNB_CHECK_CUDA(cudaMemcpyAsync(plan->stage_b, B_host, bb, cudaMemcpyHostToDevice, s));
+  int rc = spmm_dispatch(M, plan->stage_b, GCNB_F32, k, plan->stage_c, k, k, nullptr, 0, s);
+  if (rc != GCNB_OK) return rc;
+  GCNB_CHECK_CUDA(cudaMemcpyAsync(C_host, plan->stage_c, cb, cudaMemcpyDeviceToHost, s));
+  GCNB_CHECK_CUDA(cudaStreamSynchronize(s));
+  return GCNB_OK;
+}
+
+int gcnb_permute_rows(const float* X, const int32_t* vomp, float* out, int64_t n, int k,
+                      void* stream) {
+  GCNB_REQUIRE(n >= 0 && k >= 0, "negative size");
+  if (n == 0 || k == 0) return GCNB_OK;
+  GCNB_REQUIRE(X && vomp && out, "null pointer");
+  GCNB_REQUIRE(X != out, "gcnb_permute_rows is out of place");
+  int rc = require_gpu();
+  if (rc != GCNB_OK) return rc;
+  int dev = pointer_device(X);
+  GCNB_REQUIRE(dev >= 0, "X is not a device pointer");
+  DeviceGuard guard(dev);
+  GCNB_CHECK_CUDA(guard.status);
+  const int vec4 = (k % 4 == 0) && aligned(X, 16) && aligned(out, 16);
+  const int64_t blocks = (n + 7) / 8;
+  permute_rows_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(X, vomp, out, n, k, vec4);
+  GCNB_CHECK_CUDA(cudaGetLastError());
+  return GCNB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,391 @@
+// Device side of the SpMM engine: C[m x k] = A[m x n] (CSR, fp32 values) * B[n x k].
+//
+// Replaces the reference's flexspmm_cuda_* kernels (flexspmm.cu:17-498).  Not a port: the
+// reference walks 8-row tile-segments handed out by per-SM atomic counters and atomically adds
+// partial rows; here the matrix stays in (interleaved) CSR, every output element is produced by
+// exactly one warp or one CTA, and nothing is atomic.
+//
+//   rows class  (spmm_rows_kernel)   one lane-group of G lanes per row, 32/G rows per warp.
+//                                    (col,val) pairs are fetched G at a time as one coalesced
+//                                    8-byte-per-lane load and broadcast with __shfl_sync; every
+//                                    lane owns NV vectors (128-bit where alignment allows) of the
+//                                    feature row, so one warp-wide load instruction covers a
+//                                    contiguous run of B.  U independent gathers are in flight per
+//                                    lane before the first FMA.
+//   block class (spmm_block_kernel)  rows with >= kLongRow non-zeros, cut into items of at most
+//                                    kChunk non-zeros.  One CTA per item: the item's (col,val)
+//                                    tile is staged into shared memory with one TMA bulk copy
+//                                    (cp.async.bulk + mbarrier), the 8 warps stride over the
+//                                    tile, partial rows are combined with warp shuffles and a
+//                                    shared-memory pass in fixed order.  Rows with several items
+//                                    go through a partials buffer and spmm_reduce_kernel — still
+//                                    no atomics, so results are bit-reproducible.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace gcnb {
+
+constexpr int kLongRow = 512;    // >= this many non-zeros: block class
+constexpr int kChunk = 2048;     // non-zeros per block-class work item (16 KB of smem)
+constexpr int kRowWarps = 4;     // warps per CTA, rows class
+constexpr int kBlockWarps = 8;   // warps per CTA, block class
+
+struct WorkItem {
+  int32_t row;
+  int32_t beg;   // first non-zero (index into cv)
+  int32_t end;   // one past the last
+  int32_t slot;  // -1: the item is the whole row, store to C; else index into partials
+};
+
+// ---- loads -----------------------------------------------------------------------------------
+// A stream (col,val): read once per column tile -> keep it out of L1.
+__device__ __forceinline__ int2 ld_stream_int2(const int2* p) {
+  int2 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v2.s32 {%0, %1}, [%2];"
+               : "=r"(r.x), "=r"(r.y)
+               : "l"(p));
+  return r;
+}
+
+template <typename TB, int VEC>
+struct VecLoad;
+
+template <>
+struct VecLoad<float, 4> {
+  static __device__ __forceinline__ void load(const float* p, float (&o)[4]) {
+    const float4 v = __ldg(reinterpret_cast<const float4*>(p));
+    o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w;
+  }
+};
+template <>
+struct VecLoad<float, 2> {
+  static __device__ __forceinline__ void load(const float* p, float (&o)[2]) {
+    const float2 v = __ldg(reinterpret_cast<const float2*>(p));
+    o[0] = v.x; o[1] = v.y;
+  }
+};
+template <>
+struct VecLoad<float, 1> {
+  static __device__ __forceinline__ void load(const float* p, float (&o)[1]) { o[0] = __ldg(p); }
+};
+
+__device__ __forceinline__ void bf16x2_to_f32(uint32_t w, float& lo, float& hi) {
+  lo = __uint_as_float(w << 16);
+  hi = __uint_as_float(w & 0xffff0000u);
+}
+template <>
+struct VecLoad<__nv_bfloat16, 8> {
+  static __device__ __forceinline__ void load(const __nv_bfloat16* p, float (&o)[8]) {
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
+    bf16x2_to_f32(v.x, o[0], o[1]); bf16x2_to_f32(v.y, o[2], o[3]);
+    bf16x2_to_f32(v.z, o[4], o[5]); bf16x2_to_f32(v.w, o[6], o[7]);
+  }
+};
+template <>
+struct VecLoad<__nv_bfloat16, 4> {
+  static __device__ __forceinline__ void load(const __nv_bfloat16* p, float (&o)[4]) {
+    const uint2 v = __ldg(reinterpret_cast<const uint2*>(p));
+    bf16x2_to_f32(v.x, o[0], o[1]); bf16x2_to_f32(v.y, o[2], o[3]);
+  }
+};
+template <>
+struct VecLoad<__nv_bfloat16, 2> {
+  static __device__ __forceinline__ void load(const __nv_bfloat16* p, float (&o)[2]) {
+    const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(p));
+    bf16x2_to_f32(v, o[0], o[1]);
+  }
+};
+template <>
+struct VecLoad<__nv_bfloat16, 1> {
+  static __device__ __forceinline__ void load(const __nv_bfloat16* p, float (&o)[1]) {
+    const unsigned short v = __ldg(reinterpret_cast<const unsigned short*>(p));
+    o[0] = __uint_as_float(((uint32_t)v) << 16);
+  }
+};
+
+// C is written once and not re-read by this kernel: streaming stores.
+template <int VEC>
+__device__ __forceinline__ void store_vec(float* p, const float (&v)[VEC]) {
+  if constexpr (VEC % 4 == 0) {
+#pragma unroll
+    for (int i = 0; i < VEC; i += 4)
+      __stcs(reinterpret_cast<float4*>(p + i), make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]));
+  } else if constexpr (VEC == 2) {
+    __stcs(reinterpret_cast<float2*>(p), make_float2(v[0], v[1]));
+  } else {
+    __stcs(p, v[0]);
+  }
+}
+
+__device__ __forceinline__ float epilogue(float x, const float* bias, int col, int epi) {
+  if (epi & GCNB_EPI_BIAS) x += __ldg(bias + col);
+  if (epi & GCNB_EPI_RELU) x = fmaxf(x, 0.f);
+  return x;
+}
+
+template <int NV, int VEC>
+__host__ __device__ constexpr int unroll_for() {
+  return (NV * VEC >= 16) ? 2 : (NV * VEC >= 8 ? 4 : 8);
+}
+
+// ---- rows class --------------------------------------------------------------------------------
+template <typename TB, int VEC, int G, int NV>
+__global__ void __launch_bounds__(kRowWarps * 32)
+spmm_rows_kernel(const int32_t* __restrict__ rowptr, const int2* __restrict__ cv,
+                 const TB* __restrict__ B, int64_t ldb, float* __restrict__ C, int64_t ldc,
+                 int64_t m, int k, const float* __restrict__ bias, int epi, int long_thresh) {
+  constexpr int RPW = 32 / G;
+  constexpr int U0 = unroll_for<NV, VEC>();
+  constexpr int U = U0 < G ? U0 : G;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int lig = lane & (G - 1), grp = lane / G;
+  const int64_t row = ((int64_t)blockIdx.x * kRowWarps + warp) * RPW + grp;
+  const int colbase = blockIdx.y * (G * NV * VEC);
+
+  int beg = 0, len = 0;
+  bool own = false;
+  if (row < m) {
+    beg = __ldg(rowptr + row);
+    len = __ldg(rowptr + row + 1) - beg;
+    own = len < long_thresh;
+    if (!own) len = 0;  // the block class computes this row
+  }
+  int coff[NV];
+  bool cok[NV];
+#pragma unroll
+  for (int t = 0; t < NV; ++t) {
+    coff[t] = colbase + (lig + t * G) * VEC;
+    cok[t] = coff[t] < k;
+  }
+  float acc[NV][VEC];
+#pragma unroll
+  for (int t = 0; t < NV; ++t)
+#pragma unroll
+    for (int x = 0; x < VEC; ++x) acc[t][x] = 0.f;
+
+  int maxlen = len;  // warp-uniform trip count keeps the lane groups converged
+  if constexpr (G < 32) {
+#pragma unroll
+    for (int o = G; o < 32; o <<= 1) maxlen = max(maxlen, __shfl_xor_sync(0xffffffffu, maxlen, o));
+  }
+
+  for (int base = 0; base < maxlen; base += G) {
+    int2 e = make_int2(0, 0);
+    if (base + lig < len) e = ld_stream_int2(cv + (int64_t)beg + base + lig);
+    const int cnt = min(len - base, G);       // group-uniform, may be <= 0
+    const int wcnt = min(maxlen - base, G);   // warp-uniform
+#pragma unroll
+    for (int j0 = 0; j0 < G; j0 += U) {
+      if (j0 >= wcnt) break;
+      float bv[U][NV][VEC];
+      float av[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int c = __shfl_sync(0xffffffffu, e.x, j0 + u, G);
+        const float v = __int_as_float(__shfl_sync(0xffffffffu, e.y, j0 + u, G));
+        const bool p = (j0 + u) < cnt;
+        av[u] = p ? v : 0.f;
+        const TB* bp = B + (int64_t)c * ldb;
+#pragma unroll
+        for (int t = 0; t < NV; ++t) {
+          if (p && cok[t]) {
+            VecLoad<TB, VEC>::load(bp + coff[t], bv[u][t]);
+          } else {
+#pragma unroll
+            for (int x = 0; x < VEC; ++x) bv[u][t][x] = 0.f;
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+#pragma unroll
+        for (int t = 0; t < NV; ++t)
+#pragma unroll
+          for (int x = 0; x < VEC; ++x) acc[t][x] = fmaf(av[u], bv[u][t][x], acc[t][x]);
+    }
+  }
+
+  if (own) {
+    float* crow = C + row * ldc;
+#pragma unroll
+    for (int t = 0; t < NV; ++t) {
+      if (cok[t]) {
+        float o[VEC];
+#pragma unroll
+        for (int x = 0; x < VEC; ++x) o[x] = epilogue(acc[t][x], bias, coff[t] + x, epi);
+        store_vec<VEC>(crow + coff[t], o);
+      }
+    }
+  }
+}
+
+// ---- block class -------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+
+template <typename TB, int VEC, int G, int NV>
+__global__ void __launch_bounds__(kBlockWarps * 32)
+spmm_block_kernel(const WorkItem* __restrict__ items, const int2* __restrict__ cv,
+                  const TB* __restrict__ B, int64_t ldb, float* __restrict__ C, int64_t ldc,
+                  float* __restrict__ partials, int k, const float* __restrict__ bias, int epi) {
+  constexpr int RPW = 32 / G;  // non-zeros handled per warp per step
+  constexpr int W = G * NV * VEC;
+  constexpr int U = unroll_for<NV, VEC>();
+  __shared__ alignas(16) int2 s_cv[kChunk + 2];
+  __shared__ alignas(16) float s_red[kBlockWarps][W];
+  __shared__ alignas(8) uint64_t s_bar;
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int lig = lane & (G - 1), grp = lane / G;
+  const int colbase = blockIdx.y * W;
+  const WorkItem it = items[blockIdx.x];
+
+  // One TMA bulk copy brings the item's (col,val) tile into shared memory.  Source and size must
+  // be 16-byte aligned: start one pair early when beg is odd (cv is padded by 2 pairs).
+  const int abeg = it.beg & ~1;
+  const uint32_t bytes = (uint32_t)(((it.end - abeg) * 8 + 15) & ~15);
+  const uint32_t bar = smem_u32(&s_bar);
+  if (tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (tid == 0) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
+                 : "memory");
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+        ::"r"(smem_u32(s_cv)), "l"(cv + abeg), "r"(bytes), "r"(bar)
+        : "memory");
+  }
+  {
+    uint32_t done = 0;
+    while (!done) {
+      asm volatile(
+          "{\n\t.reg .pred p;\n\t"
+          "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\t"
+          "selp.u32 %0, 1, 0, p;\n\t}"
+          : "=r"(done)
+          : "r"(bar)
+          : "memory");
+    }
+  }
+
+  int coff[NV];
+  bool cok[NV];
+#pragma unroll
+  for (int t = 0; t < NV; ++t) {
+    coff[t] = colbase + (lig + t * G) * VEC;
+    cok[t] = coff[t] < k;
+  }
+  float acc[NV][VEC];
+#pragma unroll
+  for (int t = 0; t < NV; ++t)
+#pragma unroll
+    for (int x = 0; x < VEC; ++x) acc[t][x] = 0.f;
+
+  const int off = it.beg - abeg;
+  const int n = it.end - it.beg;
+  constexpr int stride = kBlockWarps * RPW;
+  const int j_first = warp * RPW + grp;
+  for (int j0 = 0; j0 < n; j0 += stride * U) {
+    float bv[U][NV][VEC];
+    float av[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int j = j0 + u * stride + j_first;
+      const bool p = j < n;
+      const int2 e = p ? s_cv[off + j] : make_int2(0, 0);
+      av[u] = p ? __int_as_float(e.y) : 0.f;
+      const TB* bp = B + (int64_t)e.x * ldb;
+#pragma unroll
+      for (int t = 0; t < NV; ++t) {
+        if (p && cok[t]) {
+          VecLoad<TB, VEC>::load(bp + coff[t], bv[u][t]);
+        } else {
+#pragma unroll
+          for (int x = 0; x < VEC; ++x) bv[u][t][x] = 0.f;
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+#pragma unroll
+      for (int t = 0; t < NV; ++t)
+#pragma unroll
+        for (int x = 0; x < VEC; ++x) acc[t][x] = fmaf(av[u], bv[u][t][x], acc[t][x]);
+  }
+
+  // lane groups of one warp hold different non-zeros of the same row: fold them
+  if constexpr (G < 32) {
+#pragma unroll
+    for (int o = G; o < 32; o <<= 1)
+#pragma unroll
+      for (int t = 0; t < NV; ++t)
+#pragma unroll
+        for (int x = 0; x < VEC; ++x) acc[t][x] += __shfl_xor_sync(0xffffffffu, acc[t][x], o);
+  }
+  if (grp == 0) {
+#pragma unroll
+    for (int t = 0; t < NV; ++t)
+#pragma unroll
+      for (int x = 0; x < VEC; ++x) s_red[warp][(lig + t * G) * VEC + x] = acc[t][x];
+  }
+  __syncthreads();
+  for (int i = tid; i < W; i += kBlockWarps * 32) {
+    const int col = colbase + i;
+    if (col < k) {
+      float s = s_red[0][i];
+#pragma unroll
+      for (int w = 1; w < kBlockWarps; ++w) s += s_red[w][i];
+      if (it.slot < 0)
+        __stcs(C + (int64_t)it.row * ldc + col, epilogue(s, bias, col, epi));
+      else
+        partials[(int64_t)it.slot * k + col] = s;
+    }
+  }
+}
+
+// rows that were cut into several items: sum their partial rows in item order
+__global__ void __launch_bounds__(128)
+spmm_reduce_kernel(const int32_t* __restrict__ split_rows, const int32_t* __restrict__ split_ptr,
+                   const float* __restrict__ partials, float* __restrict__ C, int64_t ldc, int k,
+                   const float* __restrict__ bias, int epi) {
+  const int s = blockIdx.x;
+  const int64_t row = split_rows[s];
+  const int p0 = split_ptr[s], p1 = split_ptr[s + 1];
+  for (int col = threadIdx.x; col < k; col += blockDim.x) {
+    float v = 0.f;
+    for (int p = p0; p < p1; ++p) v += partials[(int64_t)p * k + col];
+    __stcs(C + row * ldc + col, epilogue(v, bias, col, epi));
+  }
+}
+
+// (col[], val[]) -> interleaved pairs, once at plan creation
+__global__ void interleave_kernel(const int32_t* __restrict__ col, const float* __restrict__ val,
+                                  int2* __restrict__ cv, int64_t nnz) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < nnz) cv[i] = make_int2(col[i], __float_as_int(val[i]));
+}
+
+// out[r,:] = X[vomp[r],:]   (replaces flexspmm_v9_permuteX + put_back, permutate.cu:3-39)
+__global__ void __launch_bounds__(256)
+permute_rows_kernel(const float* __restrict__ X, const int32_t* __restrict__ vomp,
+                    float* __restrict__ out, int64_t n, int k, int vec4) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= n) return;
+  const int64_t src = __ldg(vomp + row);
+  if (vec4) {
+    const float4* s = reinterpret_cast<const float4*>(X + src * k);
+    float4* d = reinterpret_cast<float4*>(out + row * k);
+    for (int i = lane; i < (k >> 2); i += 32) __stcs(d + i, __ldg(s + i));
+  } else {
+    for (int i = lane; i < k; i += 32) out[row * k + i] = __ldg(X + src * k + i);
+  }
+}
+
+}  // namespace gcnb
