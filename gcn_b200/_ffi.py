@@ -16,7 +16,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libgcn_b200.so")
 
 F32, BF16 = 0, 1
-EPI_NONE, EPI_BIAS, EPI_RELU = 0, 1, 2
+EPI_NONE, EPI_BIAS, EPI_RELU, EPI_ACCUM = 0, 1, 2, 4
 PLAN_DEFAULT, PLAN_ASSUME_SYMMETRIC, PLAN_NO_TRANSPOSE = 0, 1, 2
 ERR_NOGPU = -3
 
@@ -52,8 +52,8 @@ SIGNATURES = {
     "gcnb_spmm_t": (c_int, [c_void_p, c_void_p, c_int, c_int64, c_void_p, c_int64, c_int, c_void_p]),
     "gcnb_spmm_host": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
     "gcnb_permute_rows": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
-    "gcnb_xw": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int,
-                        c_int, c_void_p, c_int, c_int, c_void_p]),
+    "gcnb_xw": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_int64, c_int, c_void_p, c_int64,
+                        c_int64, c_int, c_int, c_void_p, c_int, c_int, c_void_p]),
     "gcnb_order_deg": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, c_void_p]),
     "gcnb_order_rcm": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p]),
     "gcnb_order_gorder": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, c_void_p]),

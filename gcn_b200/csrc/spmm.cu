@@ -235,7 +235,7 @@ static int check_operands(const gcnb_plan_t* plan, const void* B, int b_dtype, i
                (long long)ldb, (long long)ldc, k);
   GCNB_REQUIRE(k == 0 || (B != nullptr && C != nullptr), "B or C is null");
   GCNB_REQUIRE(!(epi & GCNB_EPI_BIAS) || bias != nullptr, "GCNB_EPI_BIAS without a bias pointer");
-  GCNB_REQUIRE((epi & ~(GCNB_EPI_BIAS | GCNB_EPI_RELU)) == 0, "unknown epilogue flags %d", epi);
+  GCNB_REQUIRE((epi & ~(GCNB_EPI_BIAS | GCNB_EPI_RELU | GCNB_EPI_ACCUM)) == 0, "unknown epilogue flags %d", epi);
   return GCNB_OK;
 }
 

@@ -213,6 +213,10 @@ spmm_rows_kernel(const int32_t* __restrict__ rowptr, const int2* __restrict__ cv
     for (int t = 0; t < NV; ++t) {
       if (cok[t]) {
         float o[VEC];
+        if (epi & GCNB_EPI_ACCUM) {
+#pragma unroll
+          for (int x = 0; x < VEC; ++x) acc[t][x] += crow[coff[t] + x];
+        }
 #pragma unroll
         for (int x = 0; x < VEC; ++x) o[x] = epilogue(acc[t][x], bias, coff[t] + x, epi);
         store_vec<VEC>(crow + coff[t], o);
@@ -341,8 +345,10 @@ spmm_block_kernel(const WorkItem* __restrict__ items, const int2* __restrict__ c
       float s = s_red[0][i];
 #pragma unroll
       for (int w = 1; w < kBlockWarps; ++w) s += s_red[w][i];
-      if (it.slot < 0)
+      if (it.slot < 0) {
+        if (epi & GCNB_EPI_ACCUM) s += C[(int64_t)it.row * ldc + col];
         __stcs(C + (int64_t)it.row * ldc + col, epilogue(s, bias, col, epi));
+      }
       else
         partials[(int64_t)it.slot * k + col] = s;
     }
@@ -358,7 +364,7 @@ spmm_reduce_kernel(const int32_t* __restrict__ split_rows, const int32_t* __rest
   const int64_t row = split_rows[s];
   const int p0 = split_ptr[s], p1 = split_ptr[s + 1];
   for (int col = threadIdx.x; col < k; col += blockDim.x) {
-    float v = 0.f;
+    float v = (epi & GCNB_EPI_ACCUM) ? C[row * ldc + col] : 0.f;
     for (int p = p0; p < p1; ++p) v += partials[(int64_t)p * k + col];
     __stcs(C + row * ldc + col, epilogue(v, bias, col, epi));
   }

@@ -1,0 +1,239 @@
+"""2-layer GCN with the reference's constructor / ``fit`` / ``forward`` / ``test`` / ``predict``
+API (pygcn/gcn5.py:146-411, flex form gcn6.py:201-557), running on the B200 SpMM engine.
+
+The immediate caller of the hot path.  Kept from the reference: argument
+names and defaults, Adam(lr, weight_decay) over all parameters, NLL loss on ``idx_train``, the
+three training loops (without validation / with validation / early stopping), and the per-dataset
+layer-2 choice (A·(XW) for pubmed/flickr, (A·X)·W otherwise, gcn5.py:160-163).  Changed on purpose:
+
+  * ``fit`` accepts an optional vertex reordering (``reorder='gorder'|'rcm'|'deg'|'dfs'|None``,
+    the module constants OVO/DFS/GOR/RBT of gcn6.py:27-30): Â is renumbered on the host
+    (bit-exact with the reference's renumber.cu), features AND labels AND index sets are permuted
+    consistently (the reference permutes idx_train but not the labels, SURVEY.md §4 defect 2).
+  * backward uses Âᵀ; ``_train_with_val`` / ``predict`` work with the same forward signature
+    (they are broken in gcn6, SURVEY.md §4 defect 4).
+  * ReLU of layer 1 is fused into the producing kernel's epilogue.
+"""
+from __future__ import annotations
+
+from copy import deepcopy
+
+import numpy as np
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+import torch.optim as optim
+
+from . import graph, ops
+from .layers import GraphConvolution, GraphConvolution2
+
+
+def accuracy(output, labels):
+    """utils.accuracy (pygcn/gcnio/util/utils.py)."""
+    preds = output.max(1)[1].type_as(labels)
+    return preds.eq(labels).double().sum() / len(labels)
+
+
+class GCN(nn.Module):
+    def __init__(self, nfeat, nhid, nclass, dataset="dataset", dropout=0.5, lr=0.01,
+                 weight_decay=5e-4, with_relu=True, with_bias=True, device=None):
+        super().__init__()
+        assert device is not None, "Please specify 'device'!"
+        self.device = torch.device(device)
+        self.nfeat = nfeat
+        self.hidden_sizes = [nhid]
+        self.nclass = nclass
+        self.dataname = dataset
+        self.gc1 = GraphConvolution(nfeat, nhid, with_bias=with_bias, name=dataset, layer="layer1")
+        if dataset in ("pubmed", "flickr"):
+            self.gc2 = GraphConvolution(nhid, nclass, with_bias=with_bias, name=dataset, layer="layer2")
+        else:
+            self.gc2 = GraphConvolution2(nhid, nclass, with_bias=with_bias, name=dataset, layer="layer2")
+        self.dropout = dropout
+        self.lr = lr
+        self.weight_decay = weight_decay if with_relu else 0
+        self.with_relu = with_relu
+        self.with_bias = with_bias
+        self.output = None
+        self.adj_norm = None
+        self.features = None
+        self.labels = None
+        self.vomp = None  # vomp[new] = old when a reordering is active
+        self.to(self.device)
+
+    def reset_timing(self):
+        pass
+
+    def forward(self, x, adj, name="dataset"):
+        """adj: normalised adjacency (torch sparse tensor on the GPU or an SpmmPlan)."""
+        x = self.gc1(x, adj, relu=self.with_relu)
+        x = F.dropout(x, self.dropout, training=self.training)
+        x = self.gc2(x, adj)
+        return F.log_softmax(x, dim=1)
+
+    def initialize(self):
+        self.gc1.reset_parameters()
+        self.gc2.reset_parameters()
+
+    # ---- data preparation ----------------------------------------------------------------------
+    def _prepare(self, features, adj, labels, normalize, reorder):
+        """-> (features on device (dense tensor or SpmmPlan), adjacency SpmmPlan, labels, vomp)."""
+        import scipy.sparse as sp
+
+        if isinstance(adj, ops.SpmmPlan):
+            if reorder:
+                raise ValueError("reorder needs the adjacency itself, not a prebuilt plan")
+            plan, vomp = adj, None
+        else:
+            if isinstance(adj, torch.Tensor):
+                a = adj.coalesce() if adj.layout == torch.sparse_coo else adj.to_sparse_coo().coalesce()
+                idx = a.indices().cpu().numpy()
+                mx = sp.csr_matrix((a.values().cpu().numpy(), (idx[0], idx[1])), shape=tuple(a.shape))
+            else:
+                mx = sp.csr_matrix(adj)
+            mx = graph.normalize_adj(mx) if normalize else mx.astype(np.float32)
+            mx.sort_indices()
+            vomp = None
+            rp, ci, va = mx.indptr, mx.indices, mx.data
+            if reorder:
+                fn = {"gorder": graph.renumber_gorder, "rcm": graph.renumber_rcm,
+                      "deg": graph.renumber_deg, "dfs": graph.renumber_dfs}[reorder]
+                rp, ci, va, vomp = fn(rp, ci, va)
+            plan = ops.SpmmPlan(rp, ci, va, mx.shape, device=self.device)
+
+        if isinstance(features, torch.Tensor) and not features.is_sparse:
+            x = features.to(self.device, torch.float32)
+            if vomp is not None:
+                x = ops.permute_rows(x, torch.from_numpy(vomp).to(self.device))
+        elif isinstance(features, ops.SpmmPlan):
+            if vomp is not None:
+                raise ValueError("reorder with prebuilt feature plan")
+            x = features
+        else:
+            if isinstance(features, torch.Tensor):
+                f = features.coalesce()
+                idx = f.indices().cpu().numpy()
+                fx = sp.csr_matrix((f.values().cpu().numpy(), (idx[0], idx[1])), shape=tuple(f.shape))
+            else:
+                fx = sp.csr_matrix(features)
+            if vomp is not None:
+                fx = fx[vomp]
+            x = ops.SpmmPlan.from_scipy(fx.astype(np.float32), device=self.device)
+
+        y = torch.as_tensor(np.asarray(labels) if not isinstance(labels, torch.Tensor) else labels)
+        y = y.to(self.device, torch.long)
+        if vomp is not None:
+            y = y[torch.from_numpy(vomp.astype(np.int64)).to(self.device)]
+        return x, plan, y, vomp
+
+    def _map_index(self, idx):
+        """Old vertex ids -> positions after reordering (permutateIdx, gcn6.py:378)."""
+        if idx is None:
+            return None
+        idx = torch.as_tensor(np.asarray(idx) if not isinstance(idx, torch.Tensor) else idx).long()
+        if self.vomp is not None:
+            rank = np.empty(len(self.vomp), dtype=np.int64)
+            rank[self.vomp] = np.arange(len(self.vomp))
+            idx = torch.from_numpy(rank)[idx.cpu()]
+        return idx.to(self.device)
+
+    def fit(self, features, adj, labels, idx_train, idx_val=None, train_iters=200, initialize=True,
+            verbose=False, normalize=True, patience=500, name="dataset", reorder=None):
+        self.device = self.gc1.weight.device
+        if self.device.type != "cuda":
+            raise RuntimeError("gcn_b200: GCN must live on a CUDA device (no CPU fallback)")
+        if initialize:
+            self.initialize()
+        self.features, self.adj_norm, self.labels, self.vomp = self._prepare(
+            features, adj, labels, normalize, reorder)
+        idx_train = self._map_index(idx_train)
+        idx_val = self._map_index(idx_val)
+        if idx_val is None:
+            self._train_without_val(self.labels, idx_train, train_iters, verbose)
+        elif patience < train_iters:
+            self._train_with_early_stopping(self.labels, idx_train, idx_val, train_iters, patience, verbose)
+        else:
+            self._train_with_val(self.labels, idx_train, idx_val, train_iters, verbose)
+
+    def _step(self, optimizer, labels, idx_train):
+        self.train()
+        optimizer.zero_grad()
+        output = self.forward(self.features, self.adj_norm)
+        loss = F.nll_loss(output[idx_train], labels[idx_train])
+        loss.backward()
+        optimizer.step()
+        return output, loss
+
+    def _train_without_val(self, labels, idx_train, train_iters, verbose):
+        optimizer = optim.Adam(self.parameters(), lr=self.lr, weight_decay=self.weight_decay)
+        output = None
+        for i in range(train_iters):
+            output, loss = self._step(optimizer, labels, idx_train)
+            if verbose and i % 10 == 0:
+                print(f"Epoch {i:3d}, training loss: {loss.item():.6f}")
+        self.output = output
+
+    def _train_with_val(self, labels, idx_train, idx_val, train_iters, verbose):
+        optimizer = optim.Adam(self.parameters(), lr=self.lr, weight_decay=self.weight_decay)
+        best_loss_val, best_acc_val = 100, 0
+        weights = deepcopy(self.state_dict())
+        for i in range(train_iters):
+            _, loss = self._step(optimizer, labels, idx_train)
+            if verbose and i % 10 == 0:
+                print(f"Epoch {i}, training loss: {loss.item()}")
+            self.eval()
+            with torch.no_grad():
+                output = self.forward(self.features, self.adj_norm)
+            loss_val = F.nll_loss(output[idx_val], labels[idx_val])
+            acc_val = accuracy(output[idx_val], labels[idx_val])
+            if best_loss_val > loss_val:
+                best_loss_val = loss_val
+                self.output = output
+                weights = deepcopy(self.state_dict())
+            if acc_val > best_acc_val:
+                best_acc_val = acc_val
+                self.output = output
+                weights = deepcopy(self.state_dict())
+        self.load_state_dict(weights)
+
+    def _train_with_early_stopping(self, labels, idx_train, idx_val, train_iters, patience, verbose):
+        optimizer = optim.Adam(self.parameters(), lr=self.lr, weight_decay=self.weight_decay)
+        early_stopping = patience
+        best_loss_val = 100
+        weights = deepcopy(self.state_dict())
+        for i in range(train_iters):
+            _, loss = self._step(optimizer, labels, idx_train)
+            if verbose and i % 10 == 0:
+                print(f"Epoch {i}, training loss: {loss.item()}")
+            self.eval()
+            with torch.no_grad():
+                output = self.forward(self.features, self.adj_norm)
+            loss_val = F.nll_loss(output[idx_val], labels[idx_val])
+            if best_loss_val > loss_val:
+                best_loss_val = loss_val
+                self.output = output
+                weights = deepcopy(self.state_dict())
+                patience = early_stopping
+            else:
+                patience -= 1
+            if i > early_stopping and patience <= 0:
+                break
+        self.load_state_dict(weights)
+
+    def test(self, idx_test):
+        self.eval()
+        with torch.no_grad():
+            output = self.predict()
+        idx_test = self._map_index(idx_test)
+        loss_test = F.nll_loss(output[idx_test], self.labels[idx_test])
+        acc_test = accuracy(output[idx_test], self.labels[idx_test])
+        print(f"Test set results: loss= {loss_test.item():.4f} accuracy= {acc_test.item():.4f}")
+        return acc_test
+
+    def predict(self, features=None, adj=None):
+        """Log-probabilities in the (possibly reordered) vertex numbering of the last ``fit``."""
+        self.eval()
+        if features is not None or adj is not None:
+            labels = self.labels if self.labels is not None else np.zeros(features.shape[0], dtype=np.int64)
+            self.features, self.adj_norm, _, self.vomp = self._prepare(features, adj, labels, True, None)
+        return self.forward(self.features, self.adj_norm)

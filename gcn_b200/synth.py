@@ -1,0 +1,154 @@
+"""Synthetic graphs of the shapes BASELINE.json names: there is no network for the
+real datasets, so every measurement runs on seeded random graphs with the same vertex / edge
+counts.  Generation happens with torch on whatever device is given (the GPU for the large shapes —
+it is input preparation, not the measured path) and returns the normalised adjacency
+Â = D^-½ (A + I) D^-½ as a host CSR (int32 rowptr/col, fp32 values, ascending columns): what
+utils.normalize_adj + to_sparse_csr produce in the reference (pygcn/gcnio/util/utils.py:78-90,
+gcn6.py:302-312).  Values are computed in fp64 and cast to fp32 like the reference does.
+
+Shapes (undirected edge counts before the self-loops are added):
+  cora      n=2 708        5 278 edges    Erdős–Rényi pairs
+  arxiv     n=169 343      1 166 243      random pairs, symmetrised
+  reddit    n=232 965      57.3 M         Chung-Lu power law (exponent 2.1)
+  products  n=2 449 029    61.86 M        power-law degrees, community-local endpoints (see
+                                          `local_powerlaw`): co-purchase graphs are strongly
+                                          clustered; ids are community-contiguous
+  rmat      n=2^scale      ef·n           R-MAT (a,b,c,d) = (.57,.19,.19,.05), Graph500 style
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+SEED = 15  # the reference's seed (profiling_gcn.py:76-80)
+
+SHAPES = {
+    "cora": dict(n=2708, edges=5278, kind="er"),
+    "arxiv": dict(n=169_343, edges=1_166_243, kind="er"),
+    "reddit": dict(n=232_965, edges=57_300_000, kind="chung_lu", exponent=2.1),
+    "products": dict(n=2_449_029, edges=61_859_140, kind="local", exponent=2.6, p_local=0.9,
+                     window=2048),
+}
+
+
+def _gen(device, seed):
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    return g
+
+
+def _powerlaw_cdf(n, exponent, device, g):
+    # Chung-Lu weights w_i ∝ (i+1)^(-1/(γ-1)), assigned to vertices in random order
+    w = torch.arange(1, n + 1, device=device, dtype=torch.float64).pow_(-1.0 / (exponent - 1.0))
+    w = w[torch.randperm(n, device=device, generator=g)]
+    cdf = torch.cumsum(w, 0)
+    return cdf / cdf[-1]
+
+
+def _sample(cdf, count, g):
+    u = torch.rand(count, device=cdf.device, dtype=torch.float64, generator=g)
+    return torch.searchsorted(cdf, u).clamp_(max=cdf.numel() - 1)
+
+
+def edges_er(n, edges, device, seed=SEED):
+    g = _gen(device, seed)
+    return (torch.randint(0, n, (edges,), device=device, generator=g),
+            torch.randint(0, n, (edges,), device=device, generator=g))
+
+
+def edges_chung_lu(n, edges, exponent, device, seed=SEED):
+    g = _gen(device, seed)
+    cdf = _powerlaw_cdf(n, exponent, device, g)
+    return _sample(cdf, edges, g), _sample(cdf, edges, g)
+
+
+def edges_local_powerlaw(n, edges, exponent, p_local, window, device, seed=SEED):
+    """Sources by power-law weight; a fraction p_local of the destinations within a two-sided
+    geometric window around the source id (community-contiguous numbering), the rest by power-law
+    weight anywhere (hubs)."""
+    g = _gen(device, seed)
+    cdf = _powerlaw_cdf(n, exponent, device, g)
+    src = _sample(cdf, edges, g)
+    far = _sample(cdf, edges, g)
+    mag = torch.empty(edges, device=device, dtype=torch.float64).exponential_(1.0 / window, generator=g)
+    sign = torch.randint(0, 2, (edges,), device=device, generator=g) * 2 - 1
+    near = (src + sign * (mag.long() + 1)).remainder_(n)
+    pick = torch.rand(edges, device=device, generator=g) < p_local
+    return src, torch.where(pick, near, far)
+
+
+def edges_rmat(scale, edge_factor, device, abcd=(0.57, 0.19, 0.19, 0.05), seed=SEED, chunk=1 << 26):
+    n = 1 << scale
+    total = edge_factor * n
+    g = _gen(device, seed)
+    a, b, c, _ = abcd
+    srcs, dsts = [], []
+    for start in range(0, total, chunk):
+        cnt = min(chunk, total - start)
+        src = torch.zeros(cnt, dtype=torch.int64, device=device)
+        dst = torch.zeros(cnt, dtype=torch.int64, device=device)
+        for _level in range(scale):
+            r = torch.rand(cnt, device=device, generator=g)
+            sbit = (r >= a + b).long()                       # quadrants c, d: lower half of rows
+            dbit = (((r >= a) & (r < a + b)) | (r >= a + b + c)).long()   # quadrants b, d
+            src = (src << 1) | sbit
+            dst = (dst << 1) | dbit
+        srcs.append(src)
+        dsts.append(dst)
+    return torch.cat(srcs), torch.cat(dsts)
+
+
+def normalized_csr(src, dst, n, to_host=True):
+    """Symmetrise, drop duplicates and the diagonal, add I, scale by D^-½ on both sides.
+    Returns (rowptr int32, col int32, val fp32) as numpy arrays (or device tensors)."""
+    dev = src.device
+    diag = torch.arange(n, device=dev, dtype=torch.int64)
+    keep = src != dst
+    src, dst = src[keep], dst[keep]
+    key = torch.cat((src * n + dst, dst * n + src, diag * n + diag))
+    del src, dst, keep
+    key = torch.unique(key)  # sorted: row-major, ascending columns
+    row = torch.div(key, n, rounding_mode="floor")
+    col = key - row * n
+    del key
+    counts = torch.bincount(row, minlength=n)
+    rowptr = torch.zeros(n + 1, dtype=torch.int64, device=dev)
+    torch.cumsum(counts, 0, out=rowptr[1:])
+    dinv = counts.to(torch.float64).pow_(-0.5)   # row sum of (A + I) with unit weights = its nnz
+    val = (dinv[row] * dinv[col]).to(torch.float32)
+    rowptr, col = rowptr.to(torch.int32), col.to(torch.int32)
+    if not to_host:
+        return rowptr, col, val
+    return rowptr.cpu().numpy(), col.cpu().numpy(), val.cpu().numpy()
+
+
+def make_graph(name, device="cpu", seed=SEED, scale=None, edge_factor=None, shuffle=False, **over):
+    """(rowptr, col, val, n) of Â for a named shape; `rmat` takes scale / edge_factor.
+    shuffle=True relabels the vertices by a random permutation (hides any id locality, the
+    starting point of the reorder sweep)."""
+    device = torch.device(device)
+    if name == "rmat":
+        n = 1 << scale
+        src, dst = edges_rmat(scale, edge_factor, device, seed=seed)
+    else:
+        spec = dict(SHAPES[name])
+        spec.update(over)
+        n = spec["n"]
+        if spec["kind"] == "er":
+            src, dst = edges_er(n, spec["edges"], device, seed)
+        elif spec["kind"] == "chung_lu":
+            src, dst = edges_chung_lu(n, spec["edges"], spec["exponent"], device, seed)
+        else:
+            src, dst = edges_local_powerlaw(n, spec["edges"], spec["exponent"], spec["p_local"],
+                                            spec["window"], device, seed)
+    if shuffle:
+        perm = torch.randperm(n, device=device, generator=_gen(device, seed + 1))
+        src, dst = perm[src], perm[dst]
+    rowptr, col, val = normalized_csr(src, dst, n)
+    return rowptr, col, val, n
+
+
+def spmm_bytes_flops(m, n, nnz, k, b_bytes=4, c_bytes=4):
+    """Algorithmic bytes and flops of one SpMM: CSR streamed once
+    (int32 col + fp32 val + int32 rowptr), B read once, C written once."""
+    return 8 * nnz + 4 * (m + 1) + b_bytes * n * k + c_bytes * m * k, 2 * nnz * k

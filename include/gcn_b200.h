@@ -42,6 +42,8 @@ extern "C" {
 #define GCNB_EPI_NONE 0
 #define GCNB_EPI_BIAS 1
 #define GCNB_EPI_RELU 2
+#define GCNB_EPI_ACCUM 4 /* gcnb_spmm only: C = C + A·B (then bias/ReLU); used by the column-split
+                            multi-GPU path, gcn_b200/dist.py */
 
 /* plan flags */
 #define GCNB_PLAN_DEFAULT 0
@@ -96,13 +98,17 @@ int gcnb_spmm_host(gcnb_plan_t* plan, const float* B_host, float* C_host, int k,
 int gcnb_permute_rows(const float* X, const int32_t* vomp, float* out, int64_t n, int k,
                       void* stream);
 
-/* Dense feature transform on tcgen05 tensor cores:  D[M x N] = X[M x K] · W[K x N] (+bias)(ReLU).
- * Replaces torch.mm(input, self.weight) (pygcn/gcn6.py:131).  fp32 in / fp32 out; `precision`
- * 0 = 3xTF32 split (fp32-parity mode, ~1e-6 rel), 1 = single-pass TF32, 2 = bf16 operands.
- * Row-major device pointers with leading dimensions. */
-int gcnb_xw(const float* X, int64_t ldx, const float* W, int64_t ldw, float* D, int64_t ldd,
-            int64_t M, int N, int K, const float* bias, int epilogue, int precision,
-            void* stream);
+/* Dense feature transform on tcgen05 tensor cores:
+ *   D[M x N] = op(X) · op(W) (+bias[N]) (ReLU),  op(X) is M x K, op(W) is K x N.
+ * Replaces torch.mm(input, self.weight) (pygcn/gcn6.py:131, :191; gcn5.py:88, :136) and the two
+ * products autograd derives from it (dX = dS·W^T: trans_w = 1;  dW = X^T·dS: trans_x = 1).
+ * fp32 in / fp32 out, row-major DEVICE pointers with leading dimensions (elements); a set trans
+ * flag means the stored matrix is the transpose of the operand (X stored K x M, W stored N x K).
+ * `precision` 0 = 3xTF32 split (fp32-parity mode, ~1e-6 rel), 1 = single-pass TF32,
+ * 2 = bf16 operands. */
+int gcnb_xw(const float* X, int64_t ldx, int trans_x, const float* W, int64_t ldw, int trans_w,
+            float* D, int64_t ldd, int64_t M, int N, int K, const float* bias, int epilogue,
+            int precision, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Host graph preprocessing (bit-exact with the reference).  All arrays HOST memory.
