@@ -1,0 +1,356 @@
+#!/usr/bin/env python
+"""Benchmark of the GCN aggregation SpMM hot path (BASELINE.json metric: SpMM GFLOP/s and HBM GB/s
+against the roofline) on a synthetic graph of a BASELINE shape.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload products|arxiv|reddit|rmat]
+                    [--k WIDTH] [--impl ours|reference]
+
+A "step" is one pass of the hot path over the whole graph: C = Â·B (fp32), Â resident in HBM in
+the plan's layout.  Default workload: the ogbn-products-shaped graph at feature width 100 — the
+configuration BASELINE.json's target ("≥60 % of HBM roofline on ogbn-products-shaped graphs at 1
+GPU") is quoted on and the one its 1/2/4/8-GPU row-partitioned runs use.  B (≈0.98 GB) is far
+larger than L2, so every timed iteration streams from HBM; no explicit flush is needed.
+
+N > 1 (launched by torchrun, one rank per GPU): the same graph, row-partitioned by non-zeros,
+all-gather of B over NCCL overlapped with the local-column block (gcn_b200/dist.py) — strong
+scaling, value = total flops ÷ max-over-ranks device time.
+
+--impl reference: the reference's CPU implementation of the path — torch.spmm(adj, B) on COO
+tensors (pygcn/gcn1.py:53) — on the box's host cores, on a bounded row-slice sample.
+Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "spmm_gflops"
+UNIT = "GFLOP/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="products", choices=["products", "arxiv", "reddit", "rmat", "cora"])
+    ap.add_argument("--k", type=int, default=0, help="feature width (default: the shape's)")
+    ap.add_argument("--scale", type=int, default=22, help="rmat: log2 vertices")
+    ap.add_argument("--edge-factor", type=int, default=16)
+    ap.add_argument("--dtype", default="f32", choices=["f32", "bf16"])
+    ap.add_argument("--shuffle", action="store_true", help="random vertex relabelling (no id locality)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+DEFAULT_K = {"products": 100, "arxiv": 256, "reddit": 128, "rmat": 128, "cora": 16}
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.rows, self.stop, self.index = [], threading.Event(), index
+        self.thread = threading.Thread(target=self._run, daemon=True)
+
+    def _sample(self):
+        try:
+            out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                  "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
+            parts = [p.strip() for p in out.strip().split(",")]
+            if len(parts) >= 6:
+                self.rows.append(parts)
+        except Exception:
+            pass
+
+    def _run(self):
+        while not self.stop.is_set():
+            self._sample()
+            self.stop.wait(0.1)
+
+    def __enter__(self):
+        self.thread.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop.set()
+        self.thread.join(timeout=10)
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        sm = sorted(float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in self.rows)]
+        mx = [float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+def make_workload(args, device):
+    from gcn_b200 import synth
+    k = args.k or DEFAULT_K[args.workload]
+    if args.workload == "rmat":
+        rp, ci, va, n = synth.make_graph("rmat", device=device, scale=args.scale,
+                                         edge_factor=args.edge_factor, shuffle=args.shuffle)
+        name = f"rmat-s{args.scale}-ef{args.edge_factor}"
+    else:
+        rp, ci, va, n = synth.make_graph(args.workload, device=device, shuffle=args.shuffle)
+        name = f"{args.workload}-shaped"
+    return name, rp, ci, va, n, k
+
+
+def workload_string(name, k):
+    return f"{name} SpMM C=A·B fp32, k={k}"
+
+
+# ---- CPU baseline: the reference's path on the host cores ------------------------------------------
+def cpu_reference_sample(rp, ci, va, n, k, budget_s=10.0, reps=1):
+    """torch.spmm(adj, B) on CPU (pygcn/gcn1.py:53) over a bounded row slice of the same Â.
+    Returns (GFLOP/s, cores, sample description, seconds per call)."""
+    from oracle import spmm_oracle as SO
+    nnz = int(rp[-1])
+    # slice sized for roughly budget_s at a guessed 4 GFLOP/s; at least 1/64 of the rows
+    want_nnz = min(nnz, max(nnz // 64, int(budget_s * 2e9 / (2 * k))))
+    hi = int(np.searchsorted(rp, want_nnz, side="left"))
+    hi = max(1, min(n, hi))
+    z = int(rp[hi])
+    adj = SO.torch_coo(rp[: hi + 1], ci[:z], va[:z], (hi, n))
+    B = torch.randn(n, k, generator=torch.Generator().manual_seed(15))
+    SO.torch_spmm_cpu(adj, B)  # warm-up (thread pool, page faults)
+    best = float("inf")
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        SO.torch_spmm_cpu(adj, B)
+        best = min(best, time.perf_counter() - t0)
+    gflops = 2.0 * z * k / best / 1e9
+    sample = f"torch.spmm COO fp32 on rows [0,{hi}) of {n} ({z} of {nnz} nnz), k={k}, best of {reps}"
+    return gflops, torch.get_num_threads(), sample, best
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    name, rp, ci, va, n, k = make_workload(args, "cuda" if torch.cuda.is_available() else "cpu")
+    from oracle import spmm_oracle as SO
+    nnz = int(rp[-1])
+    want_nnz = min(nnz, max(nnz // 64, int(1.0 * 4e9 / (2 * k))))   # ≈1 s per step
+    hi = max(1, min(n, int(np.searchsorted(rp, want_nnz, side="left"))))
+    z = int(rp[hi])
+    adj = SO.torch_coo(rp[: hi + 1], ci[:z], va[:z], (hi, n))
+    B = torch.randn(n, k, generator=torch.Generator().manual_seed(15))
+    for _ in range(args.warmup):
+        SO.torch_spmm_cpu(adj, B)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        SO.torch_spmm_cpu(adj, B)
+    dt = (time.perf_counter() - t0) / args.steps
+    val = 2.0 * z * k / dt / 1e9
+    sample = f"torch.spmm COO fp32 (pygcn/gcn1.py:53) on rows [0,{hi}) of {n} ({z} of {nnz} nnz), k={k}"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_string(name, k), "n": n, "nnz": nnz, "k": k},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": torch.get_num_threads(),
+                         "kind": "reference", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+# ---- our arm -------------------------------------------------------------------------------------
+def time_steps(fn, steps, warmup, device, barrier=None):
+    """W untimed + K timed calls; per-step CUDA events on the launching (current) stream."""
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize(device)
+    if barrier:
+        barrier()
+    torch.cuda.synchronize(device)
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    t0 = torch.cuda.Event(enable_timing=True)
+    t1 = torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for a, b in ev:
+        a.record()
+        fn()
+        b.record()
+    t1.record()
+    torch.cuda.synchronize(device)
+    if barrier:
+        barrier()
+    per = sorted(a.elapsed_time(b) for a, b in ev)
+    return t0.elapsed_time(t1) / steps, per[len(per) // 2], per[0]
+
+
+def run_single(args):
+    from gcn_b200 import ops, synth
+    device = torch.device("cuda", 0)
+    torch.cuda.set_device(device)
+    name, rp, ci, va, n, k = make_workload(args, device)
+    nnz = int(rp[-1])
+    t0 = time.perf_counter()
+    plan = ops.SpmmPlan(rp, ci, va, (n, n), device=device, assume_symmetric=False, need_transpose=False)
+    plan_s = time.perf_counter() - t0
+    info = plan.info()
+    dt = torch.float32 if args.dtype == "f32" else torch.bfloat16
+    g = torch.Generator(device=device).manual_seed(15)
+    B = torch.randn(n, k, device=device, generator=g).to(dt)
+    C = torch.empty(n, k, device=device, dtype=torch.float32)
+    launches_per_step = 1 + (info["block_items"] > 0) + (info["rows_split"] > 0)
+
+    with ClockSampler(0) as clk:
+        ms_avg, ms_med, ms_min = time_steps(lambda: plan.spmm(B, out=C), args.steps, args.warmup, device)
+    b_bytes = 4 if args.dtype == "f32" else 2
+    abytes, flops = synth.spmm_bytes_flops(n, n, nnz, k, b_bytes=b_bytes)
+    value = flops / (ms_avg * 1e-3) / 1e9
+    peak, peak_src = peaks()
+    achieved = abytes / (ms_avg * 1e-3) / 1e9
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_avg, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
+        "config": {"workload": workload_string(name, k),
+                   "n": n, "nnz": nnz, "k": k, "max_row_nnz": info["max_row_nnz"],
+                   "order": "random relabelling" if args.shuffle else "generator order",
+                   "l2": f"operands {abytes / 1e9:.2f} GB >> 126 MB L2; no flush needed",
+                   "plan_build_s": round(plan_s, 2)},
+        "gpu_launches": launches_per_step * args.steps,
+        "ms_median": ms_med, "ms_min": ms_min,
+        "hbm_gbs_algorithmic": achieved, "pct_of_8TBs": 100 * achieved / 8000.0,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": abytes,
+                     "note": "whole-step device time (rows + block-class + reduce kernels) used as the launch duration"},
+        "clocks": clk.summary(),
+    }
+    traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(traffic_file):
+        try:
+            with open(traffic_file) as f:
+                tr = json.load(f)
+            key = f"{args.workload}-k{k}-{args.dtype}"
+            if key in tr:
+                out["roofline"]["traffic"] = tr[key]["dram_bytes_per_launch"]
+                out["roofline"]["traffic_source"] = tr[key].get("source")
+        except Exception:
+            pass
+
+    if not args.no_e2e and args.dtype == "f32":
+        # end to end through the C ABI with HOST buffers: H2D of B, SpMM, D2H of C inside the call
+        Bh = torch.randn(n, k, generator=torch.Generator().manual_seed(15)).pin_memory()
+        Ch = torch.empty(n, k).pin_memory()
+        Bn, Cn = Bh.numpy(), Ch.numpy()
+        reps = max(3, min(args.steps, 10))
+        plan.spmm_host(Bn, out=Cn)
+        torch.cuda.synchronize(device)
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            plan.spmm_host(Bn, out=Cn)     # synchronises before returning
+        e2e_s = (time.perf_counter() - t0) / reps
+        out["e2e"] = {"value": flops / e2e_s / 1e9, "unit": UNIT, "h2d_bytes_per_step": n * k * 4,
+                      "d2h_bytes_per_step": n * k * 4, "ms_per_step": e2e_s * 1e3, "steps": reps,
+                      "api": "gcnb_spmm_host (C ABI, pinned host buffers)"}
+        del Bh, Ch
+    if not args.no_cpu_baseline:
+        v, cores, sample, _ = cpu_reference_sample(rp, ci, va, n, k)
+        out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample}
+    print(json.dumps(out))
+
+
+def run_multi(args):
+    import torch.distributed as dist
+    from gcn_b200 import dist as gdist
+    from gcn_b200 import synth
+    rank = int(os.environ["RANK"])
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    world = int(os.environ["WORLD_SIZE"])
+    device = torch.device("cuda", local)
+    torch.cuda.set_device(device)
+    dist.init_process_group("nccl", device_id=device)
+    name, rp, ci, va, n, k = make_workload(args, device)   # same seed on every rank -> same graph
+    nnz = int(rp[-1])
+    part = gdist.PartitionedSpMM(rp, ci, va, n, device=device, symmetric=True)
+    local_nnz = int(part.fwd["local_csr"][0][-1])
+    remote_nnz = int(part.fwd["remote_csr"][0][-1])
+    g = torch.Generator(device=device).manual_seed(15 + rank)
+    B = torch.randn(part.m_local, k, device=device, generator=g)
+
+    def barrier():
+        dist.barrier(device_ids=[local])
+
+    with ClockSampler(local) as clk:
+        ms_avg, ms_med, ms_min = time_steps(lambda: part.forward(B), args.steps, args.warmup, device, barrier)
+    t = torch.tensor([ms_avg, ms_med, ms_min], device=device, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    stats = torch.tensor([local_nnz, remote_nnz], device=device, dtype=torch.float64)
+    dist.all_reduce(stats, op=dist.ReduceOp.SUM)
+    ms_avg, ms_med, ms_min = t.tolist()
+    if rank == 0:
+        abytes, flops = synth.spmm_bytes_flops(n, n, nnz, k)
+        peak, peak_src = peaks()
+        achieved = abytes / (ms_avg * 1e-3) / 1e9
+        gathered = (world - 1) * part.stride * k * 4
+        print(json.dumps({
+            "metric": METRIC, "value": flops / (ms_avg * 1e-3) / 1e9, "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_avg, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{name} SpMM C=A·B, k={k}, 1-D row partition by nnz over {world} GPUs, "
+                                   "NCCL all-gather of B overlapped with the local-column block",
+                       "n": n, "nnz": nnz, "k": k,
+                       "local_nnz_frac": stats[0].item() / max(nnz, 1),
+                       "allgather_bytes_received_per_rank": gathered,
+                       "l2": "operands >> L2; no flush needed"},
+            "gpu_launches": 2 * args.steps, "ms_median": ms_med, "ms_min": ms_min,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak * world, "unit": "GB/s",
+                         "frac": achieved / (peak * world), "traffic": None, "peak_source": peak_src,
+                         "note": "aggregate: algorithmic bytes of the whole SpMM over N x per-GPU HBM peak; "
+                                 "the step also moves allgather_bytes over NVLink"},
+            "clocks": clk.summary(),
+            "e2e": None,
+        }))
+    dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+        return
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the hot path is CUDA only (no CPU fallback); "
+                         "use --impl reference for the CPU reference arm")
+    if world > 1:
+        run_multi(args)
+    else:
+        run_single(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,123 @@
+"""Row-partition host logic and the exchange step of the multi-GPU path, on CPU: two `gloo`
+processes run gcn_b200.dist.PartitionedSpMM with the two device kernels replaced by the oracle
+(so what is exercised is partitioning, column remapping, padding, the all-gather and the
+local/remote accumulation order — not the CUDA kernels, which tests/test_spmm_gpu.py covers)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from conftest import random_normalized_graph, rel_err
+from gcn_b200 import dist as gdist
+from oracle import spmm_oracle as SO
+
+
+def test_bounds_balanced_and_covering():
+    A = random_normalized_graph(1000, 6000, 3, "skew")
+    for parts in (1, 2, 3, 8):
+        b = gdist.nnz_balanced_bounds(A.indptr, parts)
+        assert b[0] == 0 and b[-1] == 1000 and len(b) == parts + 1 and np.all(np.diff(b) >= 0)
+        nnz = np.diff(A.indptr[b])
+        assert nnz.sum() == A.nnz
+        assert nnz.max() <= A.nnz / parts + np.diff(A.indptr).max() + 1000 / parts + 1
+    # empty rows only
+    b = gdist.nnz_balanced_bounds(np.zeros(11, dtype=np.int32), 4)
+    assert b[0] == 0 and b[-1] == 10 and np.all(np.diff(b) >= 2)
+
+
+def test_split_local_remote_reassembles():
+    A = random_normalized_graph(301, 2500, 4)
+    n = A.shape[0]
+    rng = np.random.default_rng(0)
+    B = rng.standard_normal((n, 5)).astype(np.float32)
+    ref = SO.spmm_f64(A.indptr, A.indices, A.data, n, B)
+    parts = 3
+    bounds = gdist.nnz_balanced_bounds(A.indptr, parts)
+    stride = int(np.diff(bounds).max())
+    padded = np.zeros((parts * stride, 5), dtype=np.float32)
+    for q in range(parts):
+        padded[q * stride: q * stride + bounds[q + 1] - bounds[q]] = B[bounds[q]:bounds[q + 1]]
+    for p in range(parts):
+        local, remote, s = gdist.split_local_remote(A.indptr, A.indices, A.data, bounds, p)
+        assert s == stride
+        lo, hi = bounds[p], bounds[p + 1]
+        assert local[0][-1] + remote[0][-1] == A.indptr[hi] - A.indptr[lo]
+        assert np.all(np.diff(local[1].astype(np.int64))[np.diff(np.repeat(np.arange(hi - lo), np.diff(local[0]))) == 0] > 0)
+        C = SO.spmm_f64(*local, hi - lo, B[lo:hi]) + SO.spmm_f64(*remote, parts * stride, padded)
+        assert rel_err(C, ref[lo:hi]) < 1e-12
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+class _OraclePart(gdist.PartitionedSpMM):
+    """CPU stand-in for the two device kernels (test only)."""
+
+    def _mul_local(self, blocks, B_local, out):
+        rp, ci, va = blocks["local_csr"]
+        out.copy_(torch.from_numpy(SO.spmm_f32(rp, ci, va, self.m_local, B_local.numpy())))
+
+    def _mul_remote_accumulate(self, blocks, B_gathered, out):
+        rp, ci, va = blocks["remote_csr"]
+        out.add_(torch.from_numpy(SO.spmm_f32(rp, ci, va, B_gathered.shape[0], B_gathered.numpy())))
+
+
+def _worker(rank, world, port, symmetric, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import scipy.sparse as sp
+        A = random_normalized_graph(257, 1800, 9, "skew")
+        if not symmetric:
+            A = sp.triu(A).tocsr()
+            A.sort_indices()
+        n = A.shape[0]
+        rng = np.random.default_rng(1)
+        B = rng.standard_normal((n, 6)).astype(np.float32)
+        G = rng.standard_normal((n, 6)).astype(np.float32)
+        part = _OraclePart(A.indptr, A.indices, A.data, n, device="cpu")
+        assert part.symmetric == symmetric
+        lo, hi = part.lo, part.hi
+        Bl = torch.from_numpy(B[lo:hi].copy()).requires_grad_(True)
+        out = gdist.spmm(part, Bl)
+        out.backward(torch.from_numpy(G[lo:hi].copy()))
+        fwd = rel_err(out.detach().numpy(), SO.spmm_f64(A.indptr, A.indices, A.data, n, B)[lo:hi])
+        bwd = rel_err(Bl.grad.numpy(), SO.spmm_t_f64(A.indptr, A.indices, A.data, n, G)[lo:hi])
+        # replicated-weight gradient all-reduce
+        lin = torch.nn.Linear(2, 2)
+        lin.weight.grad = torch.full((2, 2), float(rank + 1))
+        lin.bias.grad = torch.zeros(2)
+        gdist.allreduce_grads(lin)
+        ok = bool(torch.all(lin.weight.grad == sum(range(1, world + 1))))
+        q.put((rank, fwd, bwd, ok, (lo, hi)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("symmetric", [True, False])
+def test_two_rank_gathered_spmm_gloo(symmetric):
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, symmetric, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    spans = sorted(r[4] for r in res)
+    assert spans[0][0] == 0 and spans[0][1] == spans[1][0] and spans[1][1] == 257
+    for rank, fwd, bwd, ok, _ in res:
+        assert fwd < 1e-5 and bwd < 1e-5 and ok, (rank, fwd, bwd, ok)
