@@ -1,5 +1,6 @@
 // Host side of the SpMM engine: plan construction (CSR upload, row classes, transpose), kernel
 // dispatch by feature width / dtype / alignment, the host-buffer end-to-end entry point.
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -155,8 +156,27 @@ static int launch_one(const LaunchArgs& a) {
   if (gx > 0x7fffffffLL) return set_error(GCNB_ERR_UNSUPPORTED, "too many rows for one grid");
   const int long_thresh = M.n_items > 0 ? kLongRow : 0x7fffffff;
   if (gx > 0) {
-    spmm_rows_kernel<TB, VEC, G, NV><<<dim3((unsigned)gx, ytiles), kRowWarps * 32, 0, a.stream>>>(
-        M.rowptr, M.cv, (const TB*)a.B, a.ldb, a.C, a.ldc, M.m, a.k, a.bias, a.epi, long_thresh);
+    if constexpr (G == 32) {
+      // wide feature rows: warp-per-row kernel (row pitch must fit 32 bits of bytes)
+      const int64_t gw = (M.m + kWarpRowWarps - 1) / kWarpRowWarps;
+      if (gw > 0x7fffffffLL || a.ldb * (int64_t)sizeof(TB) > 0xffffffffLL)
+        return set_error(GCNB_ERR_UNSUPPORTED, "matrix too large for one grid");
+      static const int variant = getenv("GCNB_SPMM_VARIANT") ? atoi(getenv("GCNB_SPMM_VARIANT")) : 1;
+      if (variant == 1)
+        spmm_warp_row_kernel<TB, VEC, NV, true><<<dim3((unsigned)gw, ytiles), kWarpRowWarps * 32, 0, a.stream>>>(
+            M.rowptr, M.cv, (const TB*)a.B, (uint32_t)(a.ldb * sizeof(TB)), a.C, a.ldc, M.m, a.k, a.bias,
+            a.epi, long_thresh);
+      else if (variant == 0)
+        spmm_warp_row_kernel<TB, VEC, NV, false><<<dim3((unsigned)gw, ytiles), kWarpRowWarps * 32, 0, a.stream>>>(
+            M.rowptr, M.cv, (const TB*)a.B, (uint32_t)(a.ldb * sizeof(TB)), a.C, a.ldc, M.m, a.k, a.bias,
+            a.epi, long_thresh);
+      else
+        spmm_rows_kernel<TB, VEC, G, NV><<<dim3((unsigned)gx, ytiles), kRowWarps * 32, 0, a.stream>>>(
+            M.rowptr, M.cv, (const TB*)a.B, a.ldb, a.C, a.ldc, M.m, a.k, a.bias, a.epi, long_thresh);
+    } else {
+      spmm_rows_kernel<TB, VEC, G, NV><<<dim3((unsigned)gx, ytiles), kRowWarps * 32, 0, a.stream>>>(
+          M.rowptr, M.cv, (const TB*)a.B, a.ldb, a.C, a.ldc, M.m, a.k, a.bias, a.epi, long_thresh);
+    }
     GCNB_CHECK_CUDA(cudaGetLastError());
   }
   if (M.n_items > 0) {

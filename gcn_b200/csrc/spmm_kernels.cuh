@@ -225,6 +225,182 @@ spmm_rows_kernel(const int32_t* __restrict__ rowptr, const int2* __restrict__ cv
   }
 }
 
+// ---- rows class, wide feature rows: one warp per row -------------------------------------------
+// Used when a feature row needs more than 16 lanes' worth of vectors.  Differences from the
+// lane-group kernel above, all aimed at the instruction count per non-zero (the first version spent
+// 32 issue slots per non-zero, two of them shuffles that share the LSU data pipe with the gather):
+//   * the warp's (col,val) pairs are staged 32 at a time in a private shared-memory slab and read
+//     back two pairs per LDS.128 broadcast — 0.5 instructions per non-zero instead of 2 shuffles;
+//   * the gather address is one IMAD.WIDE: per-lane base pointer + col * (row pitch in bytes);
+//   * full groups of U non-zeros run without predicates, the tail is peeled;
+//   * multiply-adds are issued as packed fma.rn.f32x2 (two lanes of fp32 per instruction).
+__device__ __forceinline__ void ffma2(float& c0, float& c1, float a, float b0, float b1) {
+  unsigned long long c, aa, bb;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(c) : "f"(c0), "f"(c1));
+  asm("mov.b64 %0, {%1, %1};" : "=l"(aa) : "f"(a));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(bb) : "f"(b0), "f"(b1));
+  asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(c) : "l"(aa), "l"(bb));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(c0), "=f"(c1) : "l"(c));
+}
+
+template <int NV, int VEC>
+__device__ __forceinline__ void fma_row(float (&acc)[NV][VEC], float a, const float (&b)[NV][VEC]) {
+#pragma unroll
+  for (int t = 0; t < NV; ++t) {
+    if constexpr (VEC % 2 == 0) {
+#pragma unroll
+      for (int x = 0; x < VEC; x += 2) ffma2(acc[t][x], acc[t][x + 1], a, b[t][x], b[t][x + 1]);
+    } else {
+#pragma unroll
+      for (int x = 0; x < VEC; ++x) acc[t][x] = fmaf(a, b[t][x], acc[t][x]);
+    }
+  }
+}
+
+constexpr int kWarpRowWarps = 8;
+
+template <typename TB, int VEC, int NV, bool PIPE>
+__global__ void __launch_bounds__(kWarpRowWarps * 32)
+spmm_warp_row_kernel(const int32_t* __restrict__ rowptr, const int2* __restrict__ cv,
+                     const TB* __restrict__ B, uint32_t ldb_bytes, float* __restrict__ C, int64_t ldc,
+                     int64_t m, int k, const float* __restrict__ bias, int epi, int long_thresh) {
+  constexpr int U0 = (NV * VEC >= 16) ? 2 : (NV * VEC >= 8 ? 4 : 8);
+  constexpr int U = (PIPE && U0 > 2) ? U0 / 2 : U0;   // two register buffers when pipelined
+  __shared__ alignas(16) int2 s_cv[kWarpRowWarps][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t row = (int64_t)blockIdx.x * kWarpRowWarps + warp;
+  if (row >= m) return;   // warp-uniform; no block-wide barrier below
+  const int colbase = blockIdx.y * (32 * NV * VEC);
+  const int beg = __ldg(rowptr + row);
+  int len = __ldg(rowptr + row + 1) - beg;
+  if (len >= long_thresh) return;   // the block class computes this row
+
+  bool cok[NV];
+  int coff[NV];
+#pragma unroll
+  for (int t = 0; t < NV; ++t) {
+    coff[t] = colbase + (lane + t * 32) * VEC;
+    cok[t] = coff[t] < k;
+  }
+  // per-lane base: out-of-range lanes are parked on column 0 and never load
+  const char* bl = reinterpret_cast<const char*>(B + (cok[0] ? coff[0] : 0));
+  float acc[NV][VEC];
+#pragma unroll
+  for (int t = 0; t < NV; ++t)
+#pragma unroll
+    for (int x = 0; x < VEC; ++x) acc[t][x] = 0.f;
+
+  int2* slab = s_cv[warp];
+  const int2* src = cv + beg;
+  int2 e = make_int2(0, 0);
+  if (lane < len) e = ld_stream_int2(src + lane);
+  for (int base = 0; base < len; base += 32) {
+    __syncwarp();               // everyone is done reading the previous slab
+    slab[lane] = e;
+    __syncwarp();
+    if (base + 32 + lane < len) e = ld_stream_int2(src + base + 32 + lane);   // prefetch the next slab
+    const int cnt = min(32, len - base);
+    int j = 0;
+    if constexpr (PIPE) {
+      // software pipeline: the gathers of group g+1 are in flight while group g is multiplied
+      // (ptxas otherwise sinks every load next to its first use and leaves ~2 loads in flight)
+      float bvA[U][NV][VEC], bvB[U][NV][VEC];
+      float avA[U], avB[U];
+      auto gather = [&](int j0, float (&bv)[U][NV][VEC], float (&av)[U]) {
+#pragma unroll
+        for (int u = 0; u < U; u += 2) {
+          const int4 q = *reinterpret_cast<const int4*>(slab + j0 + u);
+          av[u] = __int_as_float(q.y);
+          av[u + 1] = __int_as_float(q.w);
+          const char* p0 = bl + (uint64_t)(uint32_t)q.x * ldb_bytes;
+          const char* p1 = bl + (uint64_t)(uint32_t)q.z * ldb_bytes;
+#pragma unroll
+          for (int t = 0; t < NV; ++t) {
+            if (cok[t]) {
+              VecLoad<TB, VEC>::load(reinterpret_cast<const TB*>(p0) + t * 32 * VEC, bv[u][t]);
+              VecLoad<TB, VEC>::load(reinterpret_cast<const TB*>(p1) + t * 32 * VEC, bv[u + 1][t]);
+            } else {
+#pragma unroll
+              for (int x = 0; x < VEC; ++x) { bv[u][t][x] = 0.f; bv[u + 1][t][x] = 0.f; }
+            }
+          }
+        }
+      };
+      const int groups = cnt / U;
+      if (groups > 0) gather(0, bvA, avA);
+      int g = 0;
+      for (; g + 2 <= groups; g += 2) {
+        gather((g + 1) * U, bvB, avB);
+#pragma unroll
+        for (int u = 0; u < U; ++u) fma_row<NV, VEC>(acc, avA[u], bvA[u]);
+        if (g + 2 < groups) gather((g + 2) * U, bvA, avA);
+#pragma unroll
+        for (int u = 0; u < U; ++u) fma_row<NV, VEC>(acc, avB[u], bvB[u]);
+      }
+      if (g < groups) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) fma_row<NV, VEC>(acc, avA[u], bvA[u]);
+      }
+      j = groups * U;
+    } else {
+    for (; j + U <= cnt; j += U) {
+      float bv[U][NV][VEC];
+      float av[U];
+#pragma unroll
+      for (int u = 0; u < U; u += 2) {
+        const int4 q = *reinterpret_cast<const int4*>(slab + j + u);   // two pairs, broadcast
+        av[u] = __int_as_float(q.y);
+        av[u + 1] = __int_as_float(q.w);
+        const char* p0 = bl + (uint64_t)(uint32_t)q.x * ldb_bytes;
+        const char* p1 = bl + (uint64_t)(uint32_t)q.z * ldb_bytes;
+#pragma unroll
+        for (int t = 0; t < NV; ++t) {
+          if (cok[t]) {
+            VecLoad<TB, VEC>::load(reinterpret_cast<const TB*>(p0) + t * 32 * VEC, bv[u][t]);
+            VecLoad<TB, VEC>::load(reinterpret_cast<const TB*>(p1) + t * 32 * VEC, bv[u + 1][t]);
+          } else {
+#pragma unroll
+            for (int x = 0; x < VEC; ++x) { bv[u][t][x] = 0.f; bv[u + 1][t][x] = 0.f; }
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) fma_row<NV, VEC>(acc, av[u], bv[u]);
+    }
+    }
+    for (; j < cnt; ++j) {   // peeled tail, one non-zero at a time
+      const int2 q = slab[j];
+      const char* p0 = bl + (uint64_t)(uint32_t)q.x * ldb_bytes;
+      float bv[NV][VEC];
+#pragma unroll
+      for (int t = 0; t < NV; ++t) {
+        if (cok[t]) {
+          VecLoad<TB, VEC>::load(reinterpret_cast<const TB*>(p0) + t * 32 * VEC, bv[t]);
+        } else {
+#pragma unroll
+          for (int x = 0; x < VEC; ++x) bv[t][x] = 0.f;
+        }
+      }
+      fma_row<NV, VEC>(acc, __int_as_float(q.y), bv);
+    }
+  }
+
+  float* crow = C + row * ldc;
+#pragma unroll
+  for (int t = 0; t < NV; ++t) {
+    if (cok[t]) {
+      float o[VEC];
+      if (epi & GCNB_EPI_ACCUM) {
+#pragma unroll
+        for (int x = 0; x < VEC; ++x) acc[t][x] += crow[coff[t] + x];
+      }
+#pragma unroll
+      for (int x = 0; x < VEC; ++x) o[x] = epilogue(acc[t][x], bias, coff[t] + x, epi);
+      store_vec<VEC>(crow + coff[t], o);
+    }
+  }
+}
+
 // ---- block class -------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return (uint32_t)__cvta_generic_to_shared(p);

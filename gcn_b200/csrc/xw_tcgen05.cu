@@ -28,6 +28,8 @@
 //     covers the tall-K product dW = X^T·dS.
 #include <cuda_bf16.h>
 
+#include <algorithm>
+
 #include "common.h"
 
 namespace gcnb {
@@ -117,11 +119,387 @@ struct Params {
   float* D; int64_t ldd;                      // output (or partials when splits > 1)
   int64_t M; int N; int K;
   int nkb;                                    // k-blocks in total
+  int ntiles;                                 // n-tiles
   int kb_per_split;
   const float* bias; int epi;
   int x_vec;                                  // 16-byte cp.async allowed (alignment of X and ldx)
   int d_vec;                                  // 16-byte stores allowed
 };
 
+
+// ---- B operand image ---------------------------------------------------------------------------
+// image[(nt * nkb + kb)] = { part hi | part lo }, each part the canonical layout of a BN x BK tile
+// (rows = n, K-major).  MODE 0/1: tf32 bit patterns; MODE 2: bf16.  One thread per (n, k).
+template <int MODE>
+__global__ void __launch_bounds__(256)
+prep_w_kernel(const float* __restrict__ W, int64_t ldw, int trans_w, int N, int K, int bn, int nkb,
+              int ntiles, uint8_t* __restrict__ img) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t kpad = (int64_t)nkb * BK;
+  const int64_t total = (int64_t)ntiles * bn * kpad;
+  if (idx >= total) return;
+  const int64_t npad = (int64_t)ntiles * bn;
+  int k, n;   // fastest index follows the contiguous direction of the stored matrix
+  if (trans_w) { k = (int)(idx % kpad); n = (int)(idx / kpad); }
+  else         { n = (int)(idx % npad); k = (int)(idx / npad); }
+  float v = 0.f;
+  if (n < N && k < K) v = trans_w ? W[(int64_t)n * ldw + k] : W[(int64_t)k * ldw + n];
+  const int nt = n / bn, row = n % bn, kb = k / BK, kk = k % BK;
+  uint8_t* tile = img + ((int64_t)nt * nkb + kb) * (2 * b_part_bytes(bn));
+  if constexpr (MODE == 2) {
+    const int off = canon_off<8, 2>(row, kk, bn * 16);
+    *reinterpret_cast<__nv_bfloat16*>(tile + off) = __float2bfloat16_rn(v);
+  } else {
+    const int off = canon_off<4, 4>(row, kk, bn * 16);
+    const uint32_t hi = to_tf32(v);
+    *reinterpret_cast<uint32_t*>(tile + off) = hi;
+    if constexpr (MODE == 0)
+      *reinterpret_cast<uint32_t*>(tile + b_part_bytes(bn) + off) = to_tf32(v - __uint_as_float(hi));
+  }
+}
+
+// ---- main kernel ---------------------------------------------------------------------------------
+template <int BN, int MODE>
+__global__ void __launch_bounds__(THREADS)
+xw_kernel(const Params p) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  constexpr bool TF32 = MODE != 2;
+  constexpr int B_LBO = BN * 16;
+  constexpr int B_PART = b_part_bytes(BN);
+  constexpr int STAGE = stage_bytes(BN);
+  constexpr int B_BYTES = (MODE == 0 ? 2 : 1) * (TF32 ? B_PART : B_PART / 2);  // bytes the MMAs read
+  constexpr uint32_t IDESC = make_idesc(TF32 ? 2 : 1, BN);
+  constexpr int TMEM_COLS = BN <= 32 ? 32 : (BN <= 64 ? 64 : (BN <= 128 ? 128 : 256));
+
+  uint8_t* raw = smem + 2 * STAGE;                         // cp.async ring, thread-private slots
+  uint64_t* bars = reinterpret_cast<uint64_t*>(raw + RAW_STAGES * RAW_BYTES);  // [0,1] mma done, [2,3] B landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  // n-tile fastest: the CTAs that share an X tile run together, so X is fetched from HBM once
+  const int nt = (int)(blockIdx.x % p.ntiles);
+  const int64_t m0 = (int64_t)(blockIdx.x / p.ntiles) * BM;
+  const int kb0 = blockIdx.y * p.kb_per_split;
+  const int kb1 = min(p.nkb, kb0 + p.kb_per_split);
+  const int nk = kb1 - kb0;                                 // >= 1 by construction of the grid
+
+  if (tid == 0) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(bars + i)));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                 ::"r"(smem_addr(tmem_slot)), "r"(TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_d = *tmem_slot;
+
+  // ---- raw A tile: each thread owns 4 chunks (16 bytes = 4 consecutive elements of the contiguous
+  // direction) per k-block.  K-contiguous source: chunk c -> row c/4, k-chunk c%4.
+  // M-contiguous source (trans_x): chunk c -> k = c%16, m-chunk c/16 (conflict-free transposing stores).
+  auto issue_raw = [&](int kb, int slot) {
+    const int k0 = kb * BK;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int c = tid + j * THREADS;
+      const uint32_t dst = smem_addr(raw + slot * RAW_BYTES + c * 16);
+      int64_t r, q;       // element (row r of op(X), k index q), 4 elements along the contiguous direction
+      const float* src;
+      int valid;          // how many of the 4 elements are inside the matrix
+      if (!p.trans_x) {
+        r = m0 + (c >> 2); q = k0 + (c & 3) * 4;
+        valid = (r < p.M) ? max(0, min(4, p.K - (int)q)) : 0;
+        src = p.X + r * p.ldx + q;
+      } else {
+        q = k0 + (c & 15); r = m0 + (c >> 4) * 4;
+        valid = (q < p.K) ? (int)max((int64_t)0, min((int64_t)4, p.M - r)) : 0;
+        src = p.X + q * p.ldx + r;
+      }
+      if (valid == 0) {
+        cp_async16(dst, p.X, 0);                       // pure zero fill
+      } else if (p.x_vec) {
+        cp_async16(dst, src, valid * 4);
+      } else {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) cp_async4(dst + 4 * e, e < valid ? src + e : p.X, e < valid ? 4 : 0);
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+
+#pragma unroll
+  for (int s = 0; s < RAW_STAGES - 1; ++s) {
+    if (s < nk) issue_raw(kb0 + s, s);
+    else asm volatile("cp.async.commit_group;" ::: "memory");
+  }
+
+  for (int i = 0; i < nk; ++i) {
+    const int s = i & 1;
+    uint8_t* stage = smem + s * STAGE;
+    // the MMAs that read this canonical stage two iterations ago must have finished
+    if (i >= 2) {
+      mbar_wait(smem_addr(bars + s), ((i >> 1) - 1) & 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    }
+    if (tid == 0) {   // B block: one TMA bulk copy of the prepared image
+      const uint8_t* src = p.w_img + ((int64_t)nt * p.nkb + kb0 + i) * (2 * B_PART);
+      const uint32_t bar = smem_addr(bars + 2 + s);
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(B_BYTES) : "memory");
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   ::"r"(smem_addr(stage + 2 * A_PART)), "l"(src), "r"(B_BYTES), "r"(bar) : "memory");
+    }
+    asm volatile("cp.async.wait_group %0;" ::"n"(RAW_STAGES - 2) : "memory");
+    // convert this thread's own chunks into the canonical A tile(s)
+    const uint8_t* rslot = raw + (i % RAW_STAGES) * RAW_BYTES;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int c = tid + j * THREADS;
+      const float4 v = *reinterpret_cast<const float4*>(rslot + c * 16);
+      const float x[4] = {v.x, v.y, v.z, v.w};
+      if (!p.trans_x) {
+        const int row = c >> 2, k = (c & 3) * 4;
+        if constexpr (TF32) {
+          uint32_t hi[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) hi[e] = to_tf32(x[e]);
+          const int off = canon_off<4, 4>(row, k, A_LBO);
+          *reinterpret_cast<uint4*>(stage + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+          if constexpr (MODE == 0) {
+            uint32_t lo[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) lo[e] = to_tf32(x[e] - __uint_as_float(hi[e]));
+            *reinterpret_cast<uint4*>(stage + A_PART + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+          }
+        } else {
+          const __nv_bfloat162 a = __floats2bfloat162_rn(x[0], x[1]), b = __floats2bfloat162_rn(x[2], x[3]);
+          const int off = canon_off<8, 2>(row, k, A_LBO);
+          *reinterpret_cast<uint2*>(stage + off) =
+              make_uint2(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b));
+        }
+      } else {
+        const int k = c & 15, row0 = (c >> 4) * 4;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          if constexpr (TF32) {
+            const int off = canon_off<4, 4>(row0 + e, k, A_LBO);
+            const uint32_t hi = to_tf32(x[e]);
+            *reinterpret_cast<uint32_t*>(stage + off) = hi;
+            if constexpr (MODE == 0)
+              *reinterpret_cast<uint32_t*>(stage + A_PART + off) = to_tf32(x[e] - __uint_as_float(hi));
+          } else {
+            *reinterpret_cast<__nv_bfloat16*>(stage + canon_off<8, 2>(row0 + e, k, A_LBO)) =
+                __float2bfloat16_rn(x[e]);
+          }
+        }
+      }
+    }
+    // refill the ring slot consumed one iteration ago (this thread's own slot: no hazard)
+    if (i + RAW_STAGES - 1 < nk) issue_raw(kb0 + i + RAW_STAGES - 1, (i + RAW_STAGES - 1) % RAW_STAGES);
+    else asm volatile("cp.async.commit_group;" ::: "memory");
+    // generic-proxy stores -> visible to the tensor core's async proxy
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (tid == 0) {
+      mbar_wait(smem_addr(bars + 2 + s), (i >> 1) & 1);    // B block landed
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const uint32_t a_hi = smem_addr(stage), a_lo = a_hi + A_PART;
+      const uint32_t b_hi = smem_addr(stage + 2 * A_PART), b_lo = b_hi + (TF32 ? B_PART : 0);
+      constexpr int NMMA = TF32 ? BK / 8 : BK / 16;        // MMAs per part per stage (K = 32 bytes each)
+#pragma unroll
+      for (int kk = 0; kk < NMMA; ++kk) {
+        const uint32_t ao = kk * 2 * A_LBO, bo = kk * 2 * B_LBO;   // two 16-byte k-chunks per MMA
+        const uint32_t first = (i > 0 || kk > 0) ? 1u : 0u;
+        mma<TF32>(tmem_d, make_desc(a_hi + ao, A_LBO, 128), make_desc(b_hi + bo, B_LBO, 128), IDESC, first);
+        if constexpr (MODE == 0) {
+          mma<TF32>(tmem_d, make_desc(a_hi + ao, A_LBO, 128), make_desc(b_lo + bo, B_LBO, 128), IDESC, 1u);
+          mma<TF32>(tmem_d, make_desc(a_lo + ao, A_LBO, 128), make_desc(b_hi + bo, B_LBO, 128), IDESC, 1u);
+        }
+      }
+      // arrives on the mbarrier once every MMA issued so far has completed
+      asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
+                   ::"r"(smem_addr(bars + s)) : "memory");
+    }
+  }
+
+  // ---- epilogue: TMEM -> registers -> bias / ReLU -> global ------------------------------------
+  {
+    const int last = nk - 1;
+    mbar_wait(smem_addr(bars + (last & 1)), (last >> 1) & 1);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  }
+  const int64_t row = m0 + warp * 32 + lane;
+  const int ncol0 = nt * BN;
+  float* drow = p.D + ((int64_t)blockIdx.y * p.M + row) * p.ldd;   // split z writes its own partial matrix
+#pragma unroll 1
+  for (int c0 = 0; c0 < BN; c0 += 16) {
+    if (ncol0 + c0 >= p.N) break;   // warp-uniform
+    uint32_t r[16];
+    const uint32_t taddr = tmem_d + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0;
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+    if (row < p.M) {
+      float o[16];
+#pragma unroll
+      for (int e = 0; e < 16; ++e) {
+        const int col = ncol0 + c0 + e;
+        float x = __uint_as_float(r[e]);
+        if (col < p.N) {
+          if (p.epi & GCNB_EPI_BIAS) x += __ldg(p.bias + col);
+          if (p.epi & GCNB_EPI_RELU) x = fmaxf(x, 0.f);
+        }
+        o[e] = x;
+      }
+      if (p.d_vec && ncol0 + c0 + 16 <= p.N) {
+#pragma unroll
+        for (int e = 0; e < 16; e += 4)
+          *reinterpret_cast<float4*>(drow + ncol0 + c0 + e) = make_float4(o[e], o[e + 1], o[e + 2], o[e + 3]);
+      } else {
+#pragma unroll
+        for (int e = 0; e < 16; ++e)
+          if (ncol0 + c0 + e < p.N) drow[ncol0 + c0 + e] = o[e];
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 0)
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(TMEM_COLS) : "memory");
+}
+
+// split-K: D = sum_z partial[z] (+bias)(ReLU), fixed order
+__global__ void __launch_bounds__(256)
+xw_reduce_kernel(const float* __restrict__ part, int splits, int64_t M, int N, float* __restrict__ D,
+                 int64_t ldd, const float* __restrict__ bias, int epi) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= M * N) return;
+  const int64_t r = idx / N;
+  const int c = (int)(idx % N);
+  float v = 0.f;
+  for (int z = 0; z < splits; ++z) v += part[(int64_t)z * M * N + idx];
+  if (epi & GCNB_EPI_BIAS) v += __ldg(bias + c);
+  if (epi & GCNB_EPI_RELU) v = fmaxf(v, 0.f);
+  D[r * ldd + c] = v;
+}
+
 }  // namespace xw
 }  // namespace gcnb
+
+using namespace gcnb;
+
+namespace {
+
+template <int BN, int MODE>
+int launch_main(const xw::Params& p, int64_t tiles, int splits, cudaStream_t stream) {
+  static bool configured = false;   // benign race: the attribute is idempotent
+  if (!configured) {
+    GCNB_CHECK_CUDA(cudaFuncSetAttribute(xw::xw_kernel<BN, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         xw::smem_bytes(BN)));
+    configured = true;
+  }
+  xw::xw_kernel<BN, MODE><<<dim3((unsigned)tiles, (unsigned)splits), xw::THREADS, xw::smem_bytes(BN), stream>>>(p);
+  GCNB_CHECK_CUDA(cudaGetLastError());
+  return GCNB_OK;
+}
+
+template <int MODE>
+int launch_bn(int bn, const xw::Params& p, int64_t tiles, int splits, cudaStream_t stream) {
+  switch (bn) {
+    case 16: return launch_main<16, MODE>(p, tiles, splits, stream);
+    case 32: return launch_main<32, MODE>(p, tiles, splits, stream);
+    case 64: return launch_main<64, MODE>(p, tiles, splits, stream);
+    default: return launch_main<128, MODE>(p, tiles, splits, stream);
+  }
+}
+
+inline bool aligned16(const void* p) { return ((uintptr_t)p & 15) == 0; }
+
+}  // namespace
+
+extern "C" int gcnb_xw(const float* X, int64_t ldx, int trans_x, const float* W, int64_t ldw, int trans_w,
+                       float* D, int64_t ldd, int64_t M, int N, int K, const float* bias, int epilogue,
+                       int precision, void* stream_) {
+  GCNB_REQUIRE(M >= 0 && N >= 0 && K >= 0, "negative size (M=%lld N=%d K=%d)", (long long)M, N, K);
+  GCNB_REQUIRE(precision >= 0 && precision <= 2, "precision %d not in 0..2", precision);
+  GCNB_REQUIRE((epilogue & ~(GCNB_EPI_BIAS | GCNB_EPI_RELU)) == 0, "unknown epilogue flags %d", epilogue);
+  GCNB_REQUIRE(!(epilogue & GCNB_EPI_BIAS) || bias != nullptr, "GCNB_EPI_BIAS without a bias pointer");
+  if (M == 0 || N == 0) return GCNB_OK;
+  GCNB_REQUIRE(D != nullptr && ldd >= N, "D is null or ldd < N");
+  GCNB_REQUIRE(K == 0 || (X != nullptr && W != nullptr), "X or W is null");
+  GCNB_REQUIRE(K == 0 || (ldx >= (trans_x ? M : (int64_t)K) && ldw >= (trans_w ? K : N)),
+               "leading dimension smaller than the stored row length");
+  GCNB_REQUIRE(M < ((int64_t)1 << 37), "M too large");
+  int rc = require_gpu();
+  if (rc != GCNB_OK) return rc;
+  const int dev = pointer_device(D);
+  GCNB_REQUIRE(dev >= 0, "D is not a device pointer");
+  DeviceGuard guard(dev);
+  GCNB_CHECK_CUDA(guard.status);
+  cudaStream_t stream = (cudaStream_t)stream_;
+
+  if (K == 0) {   // empty sum: D = epilogue(0)
+    const int64_t total = M * N;
+    xw::xw_reduce_kernel<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(nullptr, 0, M, N, D, ldd, bias, epilogue);
+    GCNB_CHECK_CUDA(cudaGetLastError());
+    return GCNB_OK;
+  }
+
+  const int bn = N <= 16 ? 16 : (N <= 32 ? 32 : (N <= 64 ? 64 : 128));
+  const int ntiles = (N + bn - 1) / bn;
+  const int nkb = (K + xw::BK - 1) / xw::BK;
+  const int64_t mtiles = (M + xw::BM - 1) / xw::BM;
+  const int64_t tiles = mtiles * ntiles;
+  GCNB_REQUIRE(tiles < 0x7fffffffLL, "too many tiles");
+  const int n_sm = sm_count(dev);
+  int splits = 1;
+  if (tiles < 2 * n_sm && nkb > 1) splits = (int)std::min<int64_t>(nkb, (2 * n_sm + tiles - 1) / tiles);
+  const int kb_per_split = (nkb + splits - 1) / splits;
+  splits = (nkb + kb_per_split - 1) / kb_per_split;
+  GCNB_REQUIRE(splits <= 65535, "too many k splits");
+
+  uint8_t* img = nullptr;
+  float* partial = nullptr;
+  const size_t img_bytes = (size_t)ntiles * nkb * 2 * xw::b_part_bytes(bn);
+  GCNB_CHECK_CUDA(cudaMallocAsync(&img, img_bytes, stream));
+  if (precision != 0) GCNB_CHECK_CUDA(cudaMemsetAsync(img, 0, img_bytes, stream));  // unused lo parts stay defined
+  {
+    const int64_t total = (int64_t)ntiles * bn * nkb * xw::BK;
+    const unsigned blocks = (unsigned)((total + 255) / 256);
+    if (precision == 0) xw::prep_w_kernel<0><<<blocks, 256, 0, stream>>>(W, ldw, trans_w, N, K, bn, nkb, ntiles, img);
+    else if (precision == 1) xw::prep_w_kernel<1><<<blocks, 256, 0, stream>>>(W, ldw, trans_w, N, K, bn, nkb, ntiles, img);
+    else xw::prep_w_kernel<2><<<blocks, 256, 0, stream>>>(W, ldw, trans_w, N, K, bn, nkb, ntiles, img);
+    GCNB_CHECK_CUDA(cudaGetLastError());
+  }
+  xw::Params p;
+  p.X = X; p.ldx = ldx; p.trans_x = trans_x ? 1 : 0; p.w_img = img;
+  p.M = M; p.N = N; p.K = K; p.nkb = nkb; p.ntiles = ntiles; p.kb_per_split = kb_per_split;
+  p.x_vec = aligned16(X) && (ldx % 4 == 0);
+  if (splits > 1) {
+    GCNB_CHECK_CUDA(cudaMallocAsync(&partial, (size_t)splits * M * N * sizeof(float), stream));
+    p.D = partial; p.ldd = N; p.bias = nullptr; p.epi = 0;
+    p.d_vec = (N % 4 == 0);
+  } else {
+    p.D = D; p.ldd = ldd; p.bias = bias; p.epi = epilogue;
+    p.d_vec = aligned16(D) && (ldd % 4 == 0);
+  }
+  if (precision == 0) rc = launch_bn<0>(bn, p, tiles, splits, stream);
+  else if (precision == 1) rc = launch_bn<1>(bn, p, tiles, splits, stream);
+  else rc = launch_bn<2>(bn, p, tiles, splits, stream);
+  if (rc == GCNB_OK && splits > 1) {
+    const int64_t total = M * N;
+    xw::xw_reduce_kernel<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(partial, splits, M, N, D, ldd, bias, epilogue);
+    if (cudaGetLastError() != cudaSuccess) rc = set_error(GCNB_ERR_CUDA, "xw_reduce_kernel launch failed");
+  }
+  cudaFreeAsync(img, stream);
+  if (partial) cudaFreeAsync(partial, stream);
+  return rc;
+}
