@@ -51,6 +51,8 @@ def parse():
     ap.add_argument("--edge-factor", type=int, default=16)
     ap.add_argument("--dtype", default="f32", choices=["f32", "bf16"])
     ap.add_argument("--shuffle", action="store_true", help="random vertex relabelling (no id locality)")
+    ap.add_argument("--pitch", type=int, default=0,
+                    help="row pitch of B and C in elements (>= k; default k = contiguous rows)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -220,8 +222,9 @@ def run_single(args):
     info = plan.info()
     dt = torch.float32 if args.dtype == "f32" else torch.bfloat16
     g = torch.Generator(device=device).manual_seed(15)
-    B = torch.randn(n, k, device=device, generator=g).to(dt)
-    C = torch.empty(n, k, device=device, dtype=torch.float32)
+    pitch = max(args.pitch, k)
+    B = torch.randn(n, pitch, device=device, generator=g).to(dt)[:, :k]
+    C = torch.empty(n, pitch, device=device, dtype=torch.float32)[:, :k]
     launches_per_step = 1 + (info["block_items"] > 0) + (info["rows_split"] > 0)
 
     with ClockSampler(0) as clk:
@@ -238,6 +241,7 @@ def run_single(args):
         "config": {"workload": workload_string(name, k),
                    "n": n, "nnz": nnz, "k": k, "max_row_nnz": info["max_row_nnz"],
                    "order": "random relabelling" if args.shuffle else "generator order",
+                   "row_pitch_elems": pitch,
                    "l2": f"operands {abytes / 1e9:.2f} GB >> 126 MB L2; no flush needed",
                    "plan_build_s": round(plan_s, 2)},
         "gpu_launches": launches_per_step * args.steps,

@@ -18,12 +18,21 @@ struct Matrix {  // one CSR resident in HBM + its block-class work lists
   WorkItem* items = nullptr;      // [n_items]
   int32_t* split_rows = nullptr;  // [n_split] rows cut into >1 item
   int32_t* split_ptr = nullptr;   // [n_split+1] first partial slot of each split row
+  // stream class (wide feature rows): segments of ~kSegNnz non-zeros — runs of whole short rows, or
+  // pieces of one long row (their partial sums meet in spmm_reduce_kernel through s_split_*)
+  Seg* segs = nullptr;            // [n_segs]
+  int32_t* s_split_rows = nullptr;
+  int32_t* s_split_ptr = nullptr;
+  int64_t n_segs = 0, s_n_split = 0, s_n_partials = 0;
   int64_t n_items = 0, n_split = 0, n_partials = 0, n_long_rows = 0, max_row_nnz = 0;
   size_t bytes = 0;
 
   void release() {
     cudaFree(rowptr); cudaFree(cv); cudaFree(items); cudaFree(split_rows); cudaFree(split_ptr);
+    cudaFree(segs); cudaFree(s_split_rows); cudaFree(s_split_ptr);
+    s_split_rows = nullptr; s_split_ptr = nullptr;
     rowptr = nullptr; cv = nullptr; items = nullptr; split_rows = nullptr; split_ptr = nullptr;
+    segs = nullptr;
   }
 };
 
@@ -42,6 +51,15 @@ struct gcnb_plan {
 };
 
 namespace gcnb {
+
+// non-zeros per stream segment: kSegNnz on large matrices, smaller when the matrix would not give
+// every SM a few dozen segments
+static int64_t seg_target(int64_t nnz) {
+  static const int64_t forced = getenv("GCNB_SEG_NNZ") ? atoll(getenv("GCNB_SEG_NNZ")) : 0;
+  if (forced > 0) return forced;
+  const int64_t want = nnz / (148 * 64);
+  return std::max<int64_t>(64, std::min<int64_t>(kSegNnz, want));
+}
 
 static int upload_matrix(const int32_t* rowptr, const int32_t* col, const float* val, int64_t m,
                          int64_t n, int64_t nnz, Matrix* M) {
@@ -70,6 +88,45 @@ static int upload_matrix(const int32_t* rowptr, const int32_t* col, const float*
     }
   }
   split_ptr.push_back((int32_t)n_partials);
+  // stream-class segments: maximal runs of consecutive short rows, cut every ~seg_nnz non-zeros
+  // (and every 4096 rows, so that runs of empty rows are spread as well); a long row closes the run
+  // and is emitted as one segment or, beyond kSegLong non-zeros, as equal pieces with partial slots
+  std::vector<Seg> segs;
+  std::vector<int32_t> s_split_rows, s_split_ptr;
+  int64_t s_n_partials = 0;
+  {
+    const int64_t seg_nnz = seg_target(nnz);
+    int64_t r0 = -1;
+    auto close_run = [&](int64_t r_end) {
+      if (r0 >= 0) segs.push_back({(int32_t)r0, (int32_t)r_end, rowptr[r0], rowptr[r_end]});
+      r0 = -1;
+    };
+    for (int64_t r = 0; r < m; ++r) {
+      const int64_t beg = rowptr[r], end = rowptr[r + 1], len = end - beg;
+      if (len >= kLongRow) {
+        close_run(r);
+        if (len <= kSegLong) {
+          segs.push_back({(int32_t)r, (int32_t)(r + 1), (int32_t)beg, (int32_t)end});
+        } else {
+          const int64_t pieces = (len + kSegLong - 1) / kSegLong;
+          const int64_t per = (len + pieces - 1) / pieces;
+          s_split_rows.push_back((int32_t)r);
+          s_split_ptr.push_back((int32_t)s_n_partials);
+          for (int64_t b = beg; b < end; b += per)
+            segs.push_back({(int32_t)r, (int32_t)(-1 - s_n_partials++), (int32_t)b,
+                            (int32_t)std::min(end, b + per)});
+        }
+        continue;
+      }
+      if (r0 < 0) r0 = r;
+      if (end - rowptr[r0] >= seg_nnz || r + 1 - r0 >= 4096) close_run(r + 1);
+    }
+    close_run(m);
+    s_split_ptr.push_back((int32_t)s_n_partials);
+  }
+  M->s_n_split = (int64_t)s_split_rows.size();
+  M->s_n_partials = s_n_partials;
+  M->n_segs = (int64_t)segs.size();
   M->n_items = (int64_t)items.size();
   M->n_split = (int64_t)split_rows.size();
   M->n_partials = n_partials;
@@ -95,6 +152,20 @@ static int upload_matrix(const int32_t* rowptr, const int32_t* col, const float*
     GCNB_CHECK_CUDA(cudaDeviceSynchronize());
     cudaFree(d_col);
     cudaFree(d_val);
+  }
+  if (!segs.empty()) {
+    GCNB_CHECK_CUDA(cudaMalloc(&M->segs, segs.size() * sizeof(Seg)));
+    GCNB_CHECK_CUDA(cudaMemcpy(M->segs, segs.data(), segs.size() * sizeof(Seg), cudaMemcpyHostToDevice));
+    M->bytes += segs.size() * sizeof(Seg);
+  }
+  if (!s_split_rows.empty()) {
+    GCNB_CHECK_CUDA(cudaMalloc(&M->s_split_rows, s_split_rows.size() * 4));
+    GCNB_CHECK_CUDA(cudaMalloc(&M->s_split_ptr, s_split_ptr.size() * 4));
+    GCNB_CHECK_CUDA(cudaMemcpy(M->s_split_rows, s_split_rows.data(), s_split_rows.size() * 4,
+                               cudaMemcpyHostToDevice));
+    GCNB_CHECK_CUDA(cudaMemcpy(M->s_split_ptr, s_split_ptr.data(), s_split_ptr.size() * 4,
+                               cudaMemcpyHostToDevice));
+    M->bytes += (s_split_rows.size() + s_split_ptr.size()) * 4;
   }
   if (!items.empty()) {
     GCNB_CHECK_CUDA(cudaMalloc(&M->items, items.size() * sizeof(WorkItem)));
@@ -146,6 +217,44 @@ struct LaunchArgs {
   cudaStream_t stream;
 };
 
+// stream-class launch: ring depth U and CTAs/SM by registers per ring slot (NV*VEC floats + 1)
+template <typename TB, int VEC, int NV, int U, int MINB>
+static void launch_stream_cfg(const LaunchArgs& a, int64_t gs, unsigned ytiles) {
+  const Matrix& M = *a.M;
+  spmm_stream_kernel<TB, VEC, NV, U, MINB><<<dim3((unsigned)gs, ytiles), kStreamWarps * 32, 0, a.stream>>>(
+      M.segs, (int)M.n_segs, M.rowptr, M.cv, (const TB*)a.B, (uint32_t)(a.ldb * sizeof(TB)), a.C, a.ldc,
+      a.partials, a.k, a.bias, a.epi);
+}
+
+template <typename TB, int VEC, int NV>
+static int launch_stream(const LaunchArgs& a, int64_t gs, unsigned ytiles) {
+  static const int cfg = getenv("GCNB_STREAM_CFG") ? atoi(getenv("GCNB_STREAM_CFG")) : 0;
+  constexpr int F = NV * VEC;   // floats per lane per gathered row
+  if constexpr (F <= 4) {
+    switch (cfg) {
+      case 1: launch_stream_cfg<TB, VEC, NV, 4, 10>(a, gs, ytiles); break;   // 48 regs, 40 warps/SM
+      case 2: launch_stream_cfg<TB, VEC, NV, 4, 12>(a, gs, ytiles); break;   // 40 regs, 48 warps/SM
+      case 3: launch_stream_cfg<TB, VEC, NV, 8, 8>(a, gs, ytiles); break;
+      case 4: launch_stream_cfg<TB, VEC, NV, 2, 12>(a, gs, ytiles); break;
+      case 5: launch_stream_cfg<TB, VEC, NV, 8, 6>(a, gs, ytiles); break;
+      default: launch_stream_cfg<TB, VEC, NV, 4, 8>(a, gs, ytiles); break;   // 64 regs, 32 warps/SM
+    }
+  } else if constexpr (F <= 8) {
+    switch (cfg) {
+      case 1: launch_stream_cfg<TB, VEC, NV, 4, 6>(a, gs, ytiles); break;
+      case 2: launch_stream_cfg<TB, VEC, NV, 4, 5>(a, gs, ytiles); break;
+      default: launch_stream_cfg<TB, VEC, NV, 2, 8>(a, gs, ytiles); break;
+    }
+  } else {
+    switch (cfg) {
+      case 1: launch_stream_cfg<TB, VEC, NV, 2, 6>(a, gs, ytiles); break;
+      case 2: launch_stream_cfg<TB, VEC, NV, 1, 8>(a, gs, ytiles); break;
+      default: launch_stream_cfg<TB, VEC, NV, 2, 5>(a, gs, ytiles); break;
+    }
+  }
+  return GCNB_OK;
+}
+
 template <typename TB, int VEC, int G, int NV>
 static int launch_one(const LaunchArgs& a) {
   const Matrix& M = *a.M;
@@ -161,7 +270,22 @@ static int launch_one(const LaunchArgs& a) {
       const int64_t gw = (M.m + kWarpRowWarps - 1) / kWarpRowWarps;
       if (gw > 0x7fffffffLL || a.ldb * (int64_t)sizeof(TB) > 0xffffffffLL)
         return set_error(GCNB_ERR_UNSUPPORTED, "matrix too large for one grid");
-      static const int variant = getenv("GCNB_SPMM_VARIANT") ? atoi(getenv("GCNB_SPMM_VARIANT")) : 1;
+      static const int variant = getenv("GCNB_SPMM_VARIANT") ? atoi(getenv("GCNB_SPMM_VARIANT")) : 3;
+      if (variant == 3) {
+        // stream class covers every row, long ones included: one launch (+ the split-row reduction)
+        if (M.n_segs > 0) {
+          const int64_t gs = (M.n_segs + kStreamWarps - 1) / kStreamWarps;
+          int rc = launch_stream<TB, VEC, NV>(a, gs, ytiles);
+          if (rc != GCNB_OK) return rc;
+          GCNB_CHECK_CUDA(cudaGetLastError());
+          if (M.s_n_split > 0) {
+            spmm_reduce_kernel<<<(unsigned)M.s_n_split, 128, 0, a.stream>>>(
+                M.s_split_rows, M.s_split_ptr, a.partials, a.C, a.ldc, a.k, a.bias, a.epi);
+            GCNB_CHECK_CUDA(cudaGetLastError());
+          }
+        }
+        return GCNB_OK;
+      } else
       if (variant == 1)
         spmm_warp_row_kernel<TB, VEC, NV, true><<<dim3((unsigned)gw, ytiles), kWarpRowWarps * 32, 0, a.stream>>>(
             M.rowptr, M.cv, (const TB*)a.B, (uint32_t)(a.ldb * sizeof(TB)), a.C, a.ldc, M.m, a.k, a.bias,
@@ -219,8 +343,9 @@ static int spmm_dispatch(const Matrix& M, const void* B, int b_dtype, int64_t ld
                          int64_t ldc, int k, const float* bias, int epi, cudaStream_t stream) {
   if (M.m == 0 || k == 0) return GCNB_OK;
   float* partials = nullptr;
-  if (M.n_partials > 0)
-    GCNB_CHECK_CUDA(cudaMallocAsync(&partials, (size_t)M.n_partials * k * sizeof(float), stream));
+  const int64_t n_part = std::max(M.n_partials, M.s_n_partials);
+  if (n_part > 0)
+    GCNB_CHECK_CUDA(cudaMallocAsync(&partials, (size_t)n_part * k * sizeof(float), stream));
   LaunchArgs a{&M, B, ldb, C, ldc, k, bias, epi, partials, stream};
   int rc;
   // vector width: limited by k, both leading dimensions and base alignment (C is stored with

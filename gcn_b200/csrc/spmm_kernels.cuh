@@ -105,6 +105,58 @@ struct VecLoad<__nv_bfloat16, 1> {
   }
 };
 
+// Raw (unconverted) vector loads for kernels that keep gathered rows in flight in registers: the
+// bf16 -> fp32 conversion must not sit next to the load (it would wait for the data at once and
+// serialise the gathers); it happens when the slot is consumed.
+template <typename TB, int VEC>
+struct RawVec;
+template <int VEC>
+struct RawVec<float, VEC> {
+  float w[VEC];
+  __device__ __forceinline__ void load(const float* p) { VecLoad<float, VEC>::load(p, w); }
+  __device__ __forceinline__ void zero() {
+#pragma unroll
+    for (int x = 0; x < VEC; ++x) w[x] = 0.f;
+  }
+  __device__ __forceinline__ void get(float (&o)[VEC]) const {
+#pragma unroll
+    for (int x = 0; x < VEC; ++x) o[x] = w[x];
+  }
+};
+template <>
+struct RawVec<__nv_bfloat16, 8> {
+  uint4 w;
+  __device__ __forceinline__ void load(const __nv_bfloat16* p) { w = __ldg(reinterpret_cast<const uint4*>(p)); }
+  __device__ __forceinline__ void zero() { w = make_uint4(0, 0, 0, 0); }
+  __device__ __forceinline__ void get(float (&o)[8]) const {
+    bf16x2_to_f32(w.x, o[0], o[1]); bf16x2_to_f32(w.y, o[2], o[3]);
+    bf16x2_to_f32(w.z, o[4], o[5]); bf16x2_to_f32(w.w, o[6], o[7]);
+  }
+};
+template <>
+struct RawVec<__nv_bfloat16, 4> {
+  uint2 w;
+  __device__ __forceinline__ void load(const __nv_bfloat16* p) { w = __ldg(reinterpret_cast<const uint2*>(p)); }
+  __device__ __forceinline__ void zero() { w = make_uint2(0, 0); }
+  __device__ __forceinline__ void get(float (&o)[4]) const {
+    bf16x2_to_f32(w.x, o[0], o[1]); bf16x2_to_f32(w.y, o[2], o[3]);
+  }
+};
+template <>
+struct RawVec<__nv_bfloat16, 2> {
+  uint32_t w;
+  __device__ __forceinline__ void load(const __nv_bfloat16* p) { w = __ldg(reinterpret_cast<const uint32_t*>(p)); }
+  __device__ __forceinline__ void zero() { w = 0; }
+  __device__ __forceinline__ void get(float (&o)[2]) const { bf16x2_to_f32(w, o[0], o[1]); }
+};
+template <>
+struct RawVec<__nv_bfloat16, 1> {
+  unsigned short w;
+  __device__ __forceinline__ void load(const __nv_bfloat16* p) { w = __ldg(reinterpret_cast<const unsigned short*>(p)); }
+  __device__ __forceinline__ void zero() { w = 0; }
+  __device__ __forceinline__ void get(float (&o)[1]) const { o[0] = __uint_as_float(((uint32_t)w) << 16); }
+};
+
 // C is written once and not re-read by this kernel: streaming stores.
 template <int VEC>
 __device__ __forceinline__ void store_vec(float* p, const float (&v)[VEC]) {
@@ -399,6 +451,207 @@ spmm_warp_row_kernel(const int32_t* __restrict__ rowptr, const int2* __restrict_
       store_vec<VEC>(crow + coff[t], o);
     }
   }
+}
+
+// ---- rows class, wide feature rows: non-zero stream over row segments ---------------------------
+// Measured on the B200 (tools/gather_probe, tools/mlp_probe; profiles/r01_b_*.jsonl):
+//   * an SM pulls one gathered 400-byte feature row out of L2 every ~6.1 cycles at best (its
+//     64 B/cycle L2 port), but only with >= 32 warps resident;
+//   * ONE warp completes a gathered row every ~97 cycles (L2 hit) / ~295 cycles (HBM) no matter how
+//     many independent loads it has issued (U = 1..16 gave the same rate), so the parallelism has
+//     to come from the number of resident warps, not from deep per-warp unrolling;
+//   * the warp-per-row kernel above spends ~370 cycles per non-zero per warp: three dependent
+//     latencies per matrix row (rowptr -> (col,val) -> feature rows), a drain at every row end and
+//     ragged row lengths inside a CTA.
+// Here a warp owns a SEGMENT of consecutive rows (~kSegNnz non-zeros, cut on the host at plan time)
+// and treats their (col,val) pairs as one continuous stream:
+//   * a ring of U register slots holds the gathered feature rows in flight: a group of U non-zeros
+//     is multiplied out of its slots while each slot is immediately refilled with the gather of the
+//     non-zero U positions ahead — loads never drain at row ends;
+//   * row ends are warp-uniform bookkeeping: the next 32 row-end offsets sit one per lane and are
+//     broadcast by a shuffle when the stream position reaches the current row end; groups that do
+//     not contain a row end (the common case) run without any per-non-zero test;
+//   * (col,val) pairs arrive 32 at a time through a per-warp shared-memory slab (coalesced 256-byte
+//     load, prefetched one slab ahead, read back as LDS broadcasts).
+// Every output row is still produced by exactly one warp: no atomics, bit-reproducible.
+constexpr int kStreamWarps = 4;
+constexpr int kSegNnz = 768;     // target non-zeros per segment of short rows (plan time)
+constexpr int kSegLong = 1024;   // a long row is cut into pieces of at most this many non-zeros
+
+struct Seg {
+  int32_t r0;    // first row
+  int32_t r1;    // >= 0: one past the last row (whole rows, results go to C);
+                 // <  0: a piece of row r0 whose partial sums go to partials slot (-1 - r1)
+  int32_t zbeg;  // first non-zero (index into cv)
+  int32_t zend;  // one past the last
+};
+
+template <typename TB, int VEC, int NV, int U, int MINB>
+__global__ void __launch_bounds__(kStreamWarps * 32, MINB)
+spmm_stream_kernel(const Seg* __restrict__ segs, int n_segs, const int32_t* __restrict__ rowptr,
+                   const int2* __restrict__ cv, const TB* __restrict__ B, uint32_t ldb_bytes,
+                   float* __restrict__ C, int64_t ldc, float* __restrict__ partials, int k,
+                   const float* __restrict__ bias, int epi_arg) {
+  static_assert(32 % U == 0, "ring size must divide the slab");
+  __shared__ alignas(16) int2 s_cv[kStreamWarps][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int s = blockIdx.x * kStreamWarps + warp;
+  if (s >= n_segs) return;   // warp-uniform; no block-wide barrier below
+  const int4 sg = __ldg(reinterpret_cast<const int4*>(segs) + s);
+  int row = sg.x;
+  const bool piece = sg.y < 0;            // part of one long row: partial sums, no epilogue
+  const int r1 = piece ? row + 1 : sg.y;
+  const int colbase = blockIdx.y * (32 * NV * VEC);
+
+  bool cok[NV];
+  int coff[NV];
+#pragma unroll
+  for (int t = 0; t < NV; ++t) {
+    coff[t] = colbase + (lane + t * 32) * VEC;
+    cok[t] = coff[t] < k;
+  }
+  const char* bl = reinterpret_cast<const char*>(B + (cok[0] ? coff[0] : 0));
+  const int r1s = sg.y;
+
+  // row ends of rows rbase .. rbase+31, one per lane
+  int rbase = row;
+  const int z0 = sg.z;
+  const int total = sg.w - z0;
+  int rp_c = piece ? sg.w : __ldg(rowptr + min(rbase + 1 + lane, r1));
+  int rend = __shfl_sync(0xffffffffu, rp_c, 0) - z0;   // stream position at which `row` ends
+
+  float acc[NV][VEC];
+#pragma unroll
+  for (int t = 0; t < NV; ++t)
+#pragma unroll
+    for (int x = 0; x < VEC; ++x) acc[t][x] = 0.f;
+
+  auto flush = [&]() {   // write row `row`, move to the next one (warp-uniform)
+    // (addresses are rebuilt from the kernel parameters here, off the hot path, to keep the gather
+    // loop's register count down)
+    float* crow = r1s < 0 ? partials + (int64_t)(-1 - r1s) * k : C + (int64_t)row * ldc;
+    const int epi = r1s < 0 ? 0 : epi_arg;
+#pragma unroll
+    for (int t = 0; t < NV; ++t) {
+      if (cok[t]) {
+        float o[VEC];
+        if (epi & GCNB_EPI_ACCUM) {
+#pragma unroll
+          for (int x = 0; x < VEC; ++x) acc[t][x] += crow[coff[t] + x];
+        }
+#pragma unroll
+        for (int x = 0; x < VEC; ++x) o[x] = epilogue(acc[t][x], bias, coff[t] + x, epi);
+        store_vec<VEC>(crow + coff[t], o);
+      }
+#pragma unroll
+      for (int x = 0; x < VEC; ++x) acc[t][x] = 0.f;
+    }
+    ++row;
+    int idx = row - rbase;
+    if (idx == 32) {
+      rbase = row;
+      rp_c = __ldg(rowptr + min(rbase + 1 + lane, r1));
+      idx = 0;
+    }
+    rend = __shfl_sync(0xffffffffu, rp_c, idx) - z0;
+  };
+
+  float av[U];
+  RawVec<TB, VEC> bv[U][NV];
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    av[u] = 0.f;
+#pragma unroll
+    for (int t = 0; t < NV; ++t) bv[u][t].zero();
+  }
+  auto consume = [&](int u) {   // acc += av[u] * (row in slot u)
+#pragma unroll
+    for (int t = 0; t < NV; ++t) {
+      float b[VEC];
+      bv[u][t].get(b);
+      if constexpr (VEC % 2 == 0) {
+#pragma unroll
+        for (int x = 0; x < VEC; x += 2) ffma2(acc[t][x], acc[t][x + 1], av[u], b[x], b[x + 1]);
+      } else {
+#pragma unroll
+        for (int x = 0; x < VEC; ++x) acc[t][x] = fmaf(av[u], b[x], acc[t][x]);
+      }
+    }
+  };
+
+  // shared-memory address of this warp's slab, made opaque so that it stays in ONE register instead
+  // of being recomputed from %tid / the CTA's window base for every group
+  uint32_t slab_a, slab_l;
+  asm volatile("mov.u32 %0, %1;" : "=r"(slab_a) : "r"((uint32_t)__cvta_generic_to_shared(s_cv[warp])));
+  asm volatile("mov.u32 %0, %1;" : "=r"(slab_l) : "r"(slab_a + 8u * (uint32_t)lane));
+  const int2* src = cv + z0;
+  // issue side: `nxt` = stream position of the next non-zero to gather; its slab is refilled whenever
+  // nxt crosses a multiple of 32 (every earlier entry of the old slab has been issued by then)
+  int2 e = make_int2(0, 0);
+  if (lane < total) e = ld_stream_int2(src + lane);
+  auto refill = [&](int at) {   // make slab hold stream positions [at, at+32)
+    __syncwarp();
+    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(slab_l), "r"(e.x), "r"(e.y) : "memory");
+    __syncwarp();
+    if (at + 32 + lane < total) e = ld_stream_int2(src + at + 32 + lane);
+  };
+  auto gather = [&](int u, int c, int vbits) {
+    av[u] = __int_as_float(vbits);
+    const char* p0 = bl + (uint64_t)(uint32_t)c * ldb_bytes;
+#pragma unroll
+    for (int t = 0; t < NV; ++t)
+      if (cok[t]) bv[u][t].load(reinterpret_cast<const TB*>(p0) + t * 32 * VEC);
+  };
+  auto issue = [&](int u, int at) {   // gather non-zero `at` (valid) into ring slot u
+    int2 q;
+    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(q.x), "=r"(q.y) : "r"(slab_a + 8u * (uint32_t)(at & 31)) : "memory");
+    gather(u, q.x, q.y);
+  };
+  auto issue2 = [&](int u, int at) {   // two consecutive non-zeros (at even) with one LDS.128 broadcast
+    int4 q;
+    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(q.x), "=r"(q.y), "=r"(q.z), "=r"(q.w)
+                 : "r"(slab_a + 8u * (uint32_t)(at & 31)) : "memory");
+    gather(u, q.x, q.y);
+    gather(u + 1, q.z, q.w);
+  };
+
+  // prologue: fill the ring
+  refill(0);
+#pragma unroll
+  for (int u = 0; u < U; ++u)
+    if (u < total) issue(u, u);
+
+  for (int g = 0; g < total; g += U) {   // consume [g, g+U), issue [g+U, g+2U)
+    const int nxt = g + U;
+    if ((nxt & 31) == 0 && nxt < total) refill(nxt);
+    if (g + U <= rend && nxt + U <= total) {
+      // fast path: no row end inside the group, the next group is complete
+      if constexpr (U % 2 == 0) {
+#pragma unroll
+        for (int u = 0; u < U; u += 2) {
+          consume(u);
+          consume(u + 1);
+          issue2(u, nxt + u);
+        }
+      } else {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          consume(u);
+          issue(u, nxt + u);
+        }
+      }
+    } else {
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (g + u < total) {
+          while (g + u == rend) flush();
+          consume(u);
+        }
+        if (nxt + u < total) issue(u, nxt + u);
+      }
+    }
+  }
+  while (row < r1) flush();   // the last row of the segment and any trailing empty rows
 }
 
 // ---- block class -------------------------------------------------------------------------------

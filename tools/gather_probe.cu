@@ -14,11 +14,11 @@
 
 template <int U, int VB>   // VB = bytes per lane per load (16, 8, 4)
 __global__ void gather_kernel(const char* __restrict__ table, const int* __restrict__ idx, int per_warp,
-                              int row_bytes, float* __restrict__ out) {
+                              int row_bytes, int act_bytes, float* __restrict__ out) {
   const int lane = threadIdx.x & 31;
   const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int* my = idx + (size_t)gw * per_warp;
-  const bool act = lane * VB < row_bytes;
+  const bool act = lane * VB < act_bytes;
   float acc[4] = {0.f, 0.f, 0.f, 0.f};
   for (int i = 0; i < per_warp; i += 32) {
     const int mine = my[i + lane];
@@ -52,12 +52,12 @@ __global__ void stream_kernel(const float4* __restrict__ t, size_t n4, float* ou
 }
 
 template <int U, int VB>
-float run(const char* table, const int* idx, int per_warp, int row_bytes, float* out, int grid, int block) {
+float run(const char* table, const int* idx, int per_warp, int row_bytes, int act_bytes, float* out, int grid, int block) {
   cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b);
-  for (int i = 0; i < 2; ++i) gather_kernel<U, VB><<<grid, block>>>(table, idx, per_warp, row_bytes, out);
+  for (int i = 0; i < 2; ++i) gather_kernel<U, VB><<<grid, block>>>(table, idx, per_warp, row_bytes, act_bytes, out);
   CK(cudaDeviceSynchronize());
   cudaEventRecord(a);
-  for (int i = 0; i < 5; ++i) gather_kernel<U, VB><<<grid, block>>>(table, idx, per_warp, row_bytes, out);
+  for (int i = 0; i < 5; ++i) gather_kernel<U, VB><<<grid, block>>>(table, idx, per_warp, row_bytes, act_bytes, out);
   cudaEventRecord(b); CK(cudaDeviceSynchronize());
   float ms; cudaEventElapsedTime(&ms, a, b); return ms / 5;
 }
@@ -70,6 +70,7 @@ int main(int argc, char** argv) {
   const int unroll = argc > 5 ? atoi(argv[5]) : 8;
   const long window = argc > 6 ? atol(argv[6]) : 0;
   int vb = argc > 7 ? atoi(argv[7]) : 16;
+  const int act_bytes = argc > 8 ? atoi(argv[8]) : row_bytes;   // bytes of each row actually read (pitch = row_bytes)
   cudaDeviceProp prop; CK(cudaGetDeviceProperties(&prop, 0));
   const int sms = prop.multiProcessorCount;
   const size_t rows = table_mb * 1024 * 1024 / row_bytes;
@@ -95,10 +96,10 @@ int main(int argc, char** argv) {
   CK(cudaMalloc(&idx, h.size() * 4)); CK(cudaMemcpy(idx, h.data(), h.size() * 4, cudaMemcpyHostToDevice));
   CK(cudaMalloc(&out, warps * 4 + 4));
   float ms = 0;
-#define RUN(UU) (vb == 16 ? run<UU, 16>(table, idx, per_warp, row_bytes, out, grid, block) : vb == 8 ? run<UU, 8>(table, idx, per_warp, row_bytes, out, grid, block) : run<UU, 4>(table, idx, per_warp, row_bytes, out, grid, block))
+#define RUN(UU) (vb == 16 ? run<UU, 16>(table, idx, per_warp, row_bytes, act_bytes, out, grid, block) : vb == 8 ? run<UU, 8>(table, idx, per_warp, row_bytes, act_bytes, out, grid, block) : run<UU, 4>(table, idx, per_warp, row_bytes, act_bytes, out, grid, block))
   switch (unroll) { case 1: ms = RUN(1); break; case 2: ms = RUN(2); break; case 4: ms = RUN(4); break; case 8: ms = RUN(8); break; case 16: ms = RUN(16); break; default: ms = RUN(32); }
   const double gathered = (double)warps * per_warp;
-  const double bytes = gathered * row_bytes;
+  const double bytes = gathered * (act_bytes < 32 * vb ? act_bytes : 32 * vb);
   const double clk = prop.clockRate * 1e3;   // Hz (max SM clock)
   // streaming reference over the same table
   cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b);
@@ -108,9 +109,9 @@ int main(int argc, char** argv) {
   for (int i = 0; i < 5; ++i) stream_kernel<<<sms * 8, 512>>>((const float4*)table, n4, out);
   cudaEventRecord(b); CK(cudaDeviceSynchronize());
   float sms_; cudaEventElapsedTime(&sms_, a, b); sms_ /= 5;
-  printf("{\"table_mb\": %zu, \"row_bytes\": %d, \"warps_per_cta\": %d, \"ctas_per_sm\": %d, \"unroll\": %d, \"window\": %ld, \"vb\": %d, "
+  printf("{\"table_mb\": %zu, \"row_bytes\": %d, \"warps_per_cta\": %d, \"ctas_per_sm\": %d, \"unroll\": %d, \"window\": %ld, \"vb\": %d, \"act_bytes\": %d, "
          "\"ms\": %.4f, \"gather_GBps\": %.1f, \"rows_per_us\": %.1f, \"cyc_per_row_per_sm\": %.2f, \"stream_GBps\": %.1f}\n",
-         table_mb, row_bytes, wpc, cps, unroll, window, vb, ms, bytes / ms / 1e6, gathered / ms / 1e3,
+         table_mb, row_bytes, wpc, cps, unroll, window, vb, act_bytes, ms, bytes / ms / 1e6, gathered / ms / 1e3,
          ms * 1e-3 * clk * sms / gathered, (double)n4 * 16 / sms_ / 1e6);
   return 0;
 }
