@@ -53,9 +53,24 @@ def parse():
     ap.add_argument("--shuffle", action="store_true", help="random vertex relabelling (no id locality)")
     ap.add_argument("--pitch", type=int, default=0,
                     help="row pitch of B and C in elements (>= k; default k = contiguous rows)")
+    ap.add_argument("--mode", default="spmm", choices=["spmm", "epoch"],
+                    help="spmm: one C = A·B pass (headline); epoch: one 2-layer GCN training epoch")
+    ap.add_argument("--order", default="none", choices=["none", "deg", "rcm", "gorder"],
+                    help="host vertex reordering applied to the graph before the plan is built")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
+
+
+def kernel_launches_per_spmm(info, k, dtype):
+    """Kernels one gcnb_spmm call launches (spmm.cu: launch_vec / launch_one), counted from the plan."""
+    vec = 4 if dtype == "f32" else (8 if k % 8 == 0 else 4)
+    while k % vec:
+        vec //= 2
+    nvec = (k + vec - 1) // vec
+    if nvec > 16:   # whole warp per row -> stream class
+        return 1 + (info["stream_rows_split"] > 0)
+    return 1 + (info["block_items"] > 0) + (info["rows_split"] > 0)
 
 
 DEFAULT_K = {"products": 100, "arxiv": 256, "reddit": 128, "rmat": 128, "cora": 16}
@@ -123,6 +138,15 @@ def make_workload(args, device):
     else:
         rp, ci, va, n = synth.make_graph(args.workload, device=device, shuffle=args.shuffle)
         name = f"{args.workload}-shaped"
+    args.reorder_s = None
+    if args.order != "none":
+        # host preprocessing of the path (renumber.cu / order_*.cu equivalents, bit-exact): timed,
+        # reported, outside the SpMM step
+        from gcn_b200 import graph
+        fn = {"deg": graph.renumber_deg, "rcm": graph.renumber_rcm, "gorder": graph.renumber_gorder}[args.order]
+        t0 = time.perf_counter()
+        rp, ci, va, _vomp = fn(rp, ci, va)
+        args.reorder_s = round(time.perf_counter() - t0, 2)
     return name, rp, ci, va, n, k
 
 
@@ -225,7 +249,9 @@ def run_single(args):
     pitch = max(args.pitch, k)
     B = torch.randn(n, pitch, device=device, generator=g).to(dt)[:, :k]
     C = torch.empty(n, pitch, device=device, dtype=torch.float32)[:, :k]
-    launches_per_step = 1 + (info["block_items"] > 0) + (info["rows_split"] > 0)
+    # k >= 97 (more than 32 four-float vectors per row... see spmm.cu launch_vec): stream class = one
+    # launch + the split-row reduction; narrower rows: lane-group rows kernel + block class + reduction
+    launches_per_step = kernel_launches_per_spmm(info, k, args.dtype)
 
     with ClockSampler(0) as clk:
         ms_avg, ms_med, ms_min = time_steps(lambda: plan.spmm(B, out=C), args.steps, args.warmup, device)
@@ -240,7 +266,8 @@ def run_single(args):
         "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
         "config": {"workload": workload_string(name, k),
                    "n": n, "nnz": nnz, "k": k, "max_row_nnz": info["max_row_nnz"],
-                   "order": "random relabelling" if args.shuffle else "generator order",
+                   "order": ("random relabelling" if args.shuffle else "generator order")
+                            + ("" if args.order == "none" else f" -> {args.order} ({args.reorder_s} s on the host)"),
                    "row_pitch_elems": pitch,
                    "l2": f"operands {abytes / 1e9:.2f} GB >> 126 MB L2; no flush needed",
                    "plan_build_s": round(plan_s, 2)},
@@ -250,7 +277,7 @@ def run_single(args):
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": abytes,
-                     "note": "whole-step device time (rows + block-class + reduce kernels) used as the launch duration"},
+                     "note": "whole-step device time (stream kernel + split-row reduce, 99.8 % / 0.2 % in profiles/r01_d_launches_products_k100.csv) used as the launch duration"},
         "clocks": clk.summary(),
     }
     traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
@@ -285,6 +312,83 @@ def run_single(args):
         v, cores, sample, _ = cpu_reference_sample(rp, ci, va, n, k)
         out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample}
     print(json.dumps(out))
+
+
+EPOCH_SHAPES = {"cora": (1433, 16, 7), "arxiv": (128, 256, 40), "reddit": (602, 128, 41),
+                "products": (100, 256, 47), "rmat": (128, 128, 16)}
+
+
+def epoch_line(args, name, n, nnz, world, ms_avg, ms_med, ms_min, clocks, extra):
+    nfeat, nhid, nclass = EPOCH_SHAPES[args.workload]
+    out = {"metric": "gcn_epoch_ms", "value": ms_avg, "unit": "ms", "n_gpus": world, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": ms_avg, "higher_is_better": False, "scaling": "strong",
+           "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": f"{name} 2-layer GCN {nfeat}->{nhid}->{nclass} training epoch "
+                                  "(forward, NLL on 5 % of the vertices, backward, Adam); pygcn/gcn5.py:146-262",
+                      "n": n, "nnz": nnz, "l2": "operands >> L2; no flush needed"},
+           "ms_median": ms_med, "ms_min": ms_min, "clocks": clocks, "e2e": None}
+    out.update(extra)
+    return out
+
+
+def run_epoch_single(args):
+    from gcn_b200 import model as gmodel
+    from gcn_b200 import ops
+    device = torch.device("cuda", 0)
+    torch.cuda.set_device(device)
+    name, rp, ci, va, n, _ = make_workload(args, device)
+    nnz = int(rp[-1])
+    nfeat, nhid, nclass = EPOCH_SHAPES[args.workload]
+    plan = ops.SpmmPlan(rp, ci, va, (n, n), device=device, assume_symmetric=True)
+    g = torch.Generator(device=device).manual_seed(15)
+    X = torch.randn(n, nfeat, device=device, generator=g)
+    labels = torch.randint(0, nclass, (n,), device=device, generator=g)
+    idx_train = torch.arange(n // 20, device=device)
+    torch.manual_seed(15)
+    net = gmodel.GCN(nfeat, nhid, nclass, dataset=args.workload, device=device)
+    net.features, net.adj_norm, net.labels = X, plan, labels
+    opt = torch.optim.Adam(net.parameters(), lr=net.lr, weight_decay=net.weight_decay)
+    with ClockSampler(0) as clk:
+        ms_avg, ms_med, ms_min = time_steps(lambda: net._step(opt, labels, idx_train), args.steps, args.warmup, device)
+    print(json.dumps(epoch_line(args, name, n, nnz, 1, ms_avg, ms_med, ms_min, clk.summary(),
+                                {"gpu_launches": None, "note": "4 SpMMs + 6 tcgen05 GEMMs of ours per epoch; "
+                                 "dropout / log_softmax / NLL / Adam are torch elementwise kernels"})))
+
+
+def run_epoch_multi(args):
+    import torch.distributed as dist
+    from gcn_b200 import dist as gdist
+    rank = int(os.environ["RANK"])
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    world = int(os.environ["WORLD_SIZE"])
+    device = torch.device("cuda", local)
+    torch.cuda.set_device(device)
+    dist.init_process_group("nccl", device_id=device)
+    name, rp, ci, va, n, _ = make_workload(args, device)
+    nnz = int(rp[-1])
+    nfeat, nhid, nclass = EPOCH_SHAPES[args.workload]
+    part = gdist.PartitionedSpMM(rp, ci, va, n, device=device, symmetric=True)
+    g = torch.Generator(device=device).manual_seed(15 + rank)
+    X = torch.randn(part.m_local, nfeat, device=device, generator=g)
+    labels = torch.randint(0, nclass, (part.m_local,), device=device, generator=g)
+    n_train = n // 20
+    idx_train = torch.arange(max(0, min(part.hi, n_train) - part.lo), device=device)
+    net = gdist.PartitionedGCN(part, nfeat, nhid, nclass)
+
+    def barrier():
+        dist.barrier(device_ids=[local])
+
+    with ClockSampler(local) as clk:
+        ms_avg, ms_med, ms_min = time_steps(lambda: net.step(X, labels, idx_train, n_train), args.steps,
+                                            args.warmup, device, barrier)
+    t = torch.tensor([ms_avg, ms_med, ms_min], device=device, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        ms_avg, ms_med, ms_min = t.tolist()
+        print(json.dumps(epoch_line(args, name, n, nnz, world, ms_avg, ms_med, ms_min, clk.summary(),
+                                    {"gpu_launches": None, "parallelism": f"1-D row partition by nnz over {world} GPUs; "
+                                     "4 NCCL all-gathers of the dense operand + 1 gradient all-reduce per epoch"})))
+    dist.destroy_process_group()
 
 
 def run_multi(args):
@@ -350,7 +454,9 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — the hot path is CUDA only (no CPU fallback); "
                          "use --impl reference for the CPU reference arm")
-    if world > 1:
+    if args.mode == "epoch":
+        (run_epoch_multi if world > 1 else run_epoch_single)(args)
+    elif world > 1:
         run_multi(args)
     else:
         run_single(args)

@@ -237,7 +237,13 @@ static int launch_stream(const LaunchArgs& a, int64_t gs, unsigned ytiles) {
       case 3: launch_stream_cfg<TB, VEC, NV, 8, 8>(a, gs, ytiles); break;
       case 4: launch_stream_cfg<TB, VEC, NV, 2, 12>(a, gs, ytiles); break;
       case 5: launch_stream_cfg<TB, VEC, NV, 8, 6>(a, gs, ytiles); break;
-      default: launch_stream_cfg<TB, VEC, NV, 4, 8>(a, gs, ytiles); break;   // 64 regs, 32 warps/SM
+      default:
+        // measured on the products-shaped graph (profiles/r01_e_stream_cfg_sweep.jsonl): fp32 slots
+        // (4 registers) are fastest at 64 regs / 32 warps per SM, bf16 slots (2 registers) fit 48
+        // regs and gain from 40 warps per SM
+        if constexpr (sizeof(TB) == 2) launch_stream_cfg<TB, VEC, NV, 4, 10>(a, gs, ytiles);
+        else launch_stream_cfg<TB, VEC, NV, 4, 8>(a, gs, ytiles);
+        break;
     }
   } else if constexpr (F <= 8) {
     switch (cfg) {
@@ -467,6 +473,7 @@ int gcnb_plan_info(const gcnb_plan_t* plan, int64_t info[16]) {
   info[7] = plan->a.n_items; info[8] = plan->a.max_row_nnz;
   info[9] = (int64_t)(plan->a.bytes + plan->at.bytes + plan->stage_b_bytes + plan->stage_c_bytes);
   info[10] = plan->n_sm; info[11] = plan->a.n_split;
+  info[12] = plan->a.n_segs; info[13] = plan->a.s_n_split;
   return GCNB_OK;
 }
 

@@ -195,3 +195,47 @@ def _is_symmetric(rowptr, col, val, n) -> bool:
     t_rowptr, t_col, t_val = _transpose(rowptr, col, val, n)
     return (np.array_equal(t_rowptr, rowptr) and np.array_equal(t_col, col)
             and np.array_equal(t_val, np.asarray(val, dtype=np.float32)))
+
+
+class PartitionedGCN(torch.nn.Module):
+    """The reference's 2-layer GCN (pygcn/gcn5.py:146-196: gc1 = A·(X·W1)+b1, ReLU, dropout,
+    gc2 = (A·H)·W2+b2, log_softmax) on the row partition: every rank holds its row block of the
+    features, activations and labels; W1/W2/biases are replicated and their gradients all-reduced
+    (SURVEY.md §8e).  One epoch = 4 gathered SpMMs (2 forward, 2 backward) + 6 dense products."""
+
+    def __init__(self, part: PartitionedSpMM, nfeat, nhid, nclass, dropout=0.5, lr=0.01,
+                 weight_decay=5e-4, seed=15):
+        super().__init__()
+        from .layers import GraphConvolution, GraphConvolution2
+        self.part = part
+        g = torch.Generator().manual_seed(seed)   # identical replicas on every rank
+        self.gc1 = GraphConvolution(nfeat, nhid)
+        self.gc2 = GraphConvolution2(nhid, nclass)
+        for p in self.parameters():
+            stdv = 1.0 / (p.shape[-1] ** 0.5)
+            p.data.copy_((torch.rand(p.shape, generator=g) * 2 - 1) * stdv)
+        self.dropout = dropout
+        self.to(part.device)
+        self.optimizer = torch.optim.Adam(self.parameters(), lr=lr, weight_decay=weight_decay)
+
+    def forward(self, x_local):
+        from . import gemm
+        support = gemm.xw(x_local, self.gc1.weight)
+        h = torch.relu(spmm(self.part, support) + self.gc1.bias)
+        h = torch.nn.functional.dropout(h, self.dropout, training=self.training)
+        s2 = spmm(self.part, h)
+        out = gemm.xw(s2, self.gc2.weight, bias=self.gc2.bias)
+        return torch.nn.functional.log_softmax(out, dim=1)
+
+    def step(self, x_local, labels_local, idx_train_local, n_train_global):
+        """One training epoch (forward, NLL on the local training rows, backward, gradient
+        all-reduce, Adam).  Returns the local loss contribution (sum / global count)."""
+        self.train()
+        self.optimizer.zero_grad(set_to_none=True)
+        out = self.forward(x_local)
+        loss = torch.nn.functional.nll_loss(out[idx_train_local], labels_local[idx_train_local],
+                                            reduction="sum") / n_train_global
+        loss.backward()
+        allreduce_grads(self, self.part.group)
+        self.optimizer.step()
+        return loss

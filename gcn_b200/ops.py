@@ -109,7 +109,8 @@ class SpmmPlan:
         buf = (ctypes.c_int64 * 16)()
         _ffi.call("gcnb_plan_info", self._handle, buf)
         keys = ("m", "n", "nnz", "symmetric", "has_transpose", "rows_warp_class", "rows_block_class",
-                "block_items", "max_row_nnz", "device_bytes", "n_sm", "rows_split")
+                "block_items", "max_row_nnz", "device_bytes", "n_sm", "rows_split",
+                "stream_segments", "stream_rows_split")
         return {k: int(buf[i]) for i, k in enumerate(keys)}
 
     @property

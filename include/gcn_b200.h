@@ -73,7 +73,8 @@ int gcnb_plan_create(const int32_t* rowptr, const int32_t* col, const float* val
 int gcnb_plan_destroy(gcnb_plan_t* plan);
 /* info[0]=m [1]=n [2]=nnz [3]=symmetric(0/1) [4]=has_transpose [5]=rows in warp class
  * [6]=rows in block class [7]=block work items [8]=max row nnz [9]=device bytes held
- * [10]=SM count [11]=rows split across >1 block item [12..15]=reserved (0) */
+ * [10]=SM count [11]=rows split across >1 block item [12]=stream-class segments
+ * [13]=rows cut into several stream segments (they add one reduce launch) [14..15]=reserved (0) */
 int gcnb_plan_info(const gcnb_plan_t* plan, int64_t info[16]);
 
 /* C[m x k] = A · B[n x k]  (+ bias[k]) (ReLU).   Replaces flexspmm() (flexspmm.cu:499-544) and
