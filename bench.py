@@ -57,6 +57,9 @@ def parse():
                     help="spmm: one C = A·B pass (headline); epoch: one 2-layer GCN training epoch")
     ap.add_argument("--order", default="none", choices=["none", "deg", "rcm", "gorder"],
                     help="host vertex reordering applied to the graph before the plan is built")
+    ap.add_argument("--exchange", default="pull", choices=["pull", "allgather"],
+                    help="N>1: how remote feature rows arrive — our P2P halo pull over NVLink peer memory, "
+                         "or an NCCL all-gather of the whole operand")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -64,7 +67,7 @@ def parse():
 
 def kernel_launches_per_spmm(info, k, dtype):
     """Kernels one gcnb_spmm call launches (spmm.cu: launch_vec / launch_one), counted from the plan."""
-    vec = 4 if dtype == "f32" else (8 if k % 8 == 0 else 4)
+    vec = 4 if dtype == "f32" else (8 if (k % 8 == 0 and k <= 64) else 4)
     while k % vec:
         vec //= 2
     nvec = (k + vec - 1) // vec
@@ -367,7 +370,7 @@ def run_epoch_multi(args):
     name, rp, ci, va, n, _ = make_workload(args, device)
     nnz = int(rp[-1])
     nfeat, nhid, nclass = EPOCH_SHAPES[args.workload]
-    part = gdist.PartitionedSpMM(rp, ci, va, n, device=device, symmetric=True)
+    part = gdist.PartitionedSpMM(rp, ci, va, n, device=device, symmetric=True, exchange=args.exchange)
     g = torch.Generator(device=device).manual_seed(15 + rank)
     X = torch.randn(part.m_local, nfeat, device=device, generator=g)
     labels = torch.randint(0, nclass, (part.m_local,), device=device, generator=g)
@@ -387,7 +390,7 @@ def run_epoch_multi(args):
         ms_avg, ms_med, ms_min = t.tolist()
         print(json.dumps(epoch_line(args, name, n, nnz, world, ms_avg, ms_med, ms_min, clk.summary(),
                                     {"gpu_launches": None, "parallelism": f"1-D row partition by nnz over {world} GPUs; "
-                                     "4 NCCL all-gathers of the dense operand + 1 gradient all-reduce per epoch"})))
+                                     f"4 exchanges of the dense operand ({args.exchange}) + 1 gradient all-reduce per epoch"})))
     dist.destroy_process_group()
 
 
@@ -403,7 +406,7 @@ def run_multi(args):
     dist.init_process_group("nccl", device_id=device)
     name, rp, ci, va, n, k = make_workload(args, device)   # same seed on every rank -> same graph
     nnz = int(rp[-1])
-    part = gdist.PartitionedSpMM(rp, ci, va, n, device=device, symmetric=True)
+    part = gdist.PartitionedSpMM(rp, ci, va, n, device=device, symmetric=True, exchange=args.exchange)
     local_nnz = int(part.fwd["local_csr"][0][-1])
     remote_nnz = int(part.fwd["remote_csr"][0][-1])
     g = torch.Generator(device=device).manual_seed(15 + rank)
@@ -414,27 +417,43 @@ def run_multi(args):
 
     with ClockSampler(local) as clk:
         ms_avg, ms_med, ms_min = time_steps(lambda: part.forward(B), args.steps, args.warmup, device, barrier)
-    t = torch.tensor([ms_avg, ms_med, ms_min], device=device, dtype=torch.float64)
+    # the three phases of a step, each timed alone on the compute stream (untimed region of the bench):
+    # what the overlap has to hide, and what it cannot
+    blocks = part.fwd
+    out_l = torch.empty((part.m_local, k), device=device)
+    ph_local = time_steps(lambda: part._mul_local(blocks, B, out_l), 5, 2, device, barrier)[1]
+    holder = {}
+
+    def _ex():
+        holder["full"] = part._exchange(blocks, B, part._prepare(B))
+    ph_exch = time_steps(_ex, 5, 2, device, barrier)[1]
+    ph_remote = time_steps(lambda: part._mul_remote_accumulate(blocks, holder["full"], out_l), 5, 2, device, barrier)[1]
+    halo_rows = int(blocks["halo_row"].numel()) if args.exchange == "pull" else (world - 1) * part.stride
+    t = torch.tensor([ms_avg, ms_med, ms_min, ph_local, ph_exch, ph_remote, halo_rows], device=device, dtype=torch.float64)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     stats = torch.tensor([local_nnz, remote_nnz], device=device, dtype=torch.float64)
     dist.all_reduce(stats, op=dist.ReduceOp.SUM)
-    ms_avg, ms_med, ms_min = t.tolist()
+    ms_avg, ms_med, ms_min, ph_local, ph_exch, ph_remote, halo_rows = t.tolist()
     if rank == 0:
         abytes, flops = synth.spmm_bytes_flops(n, n, nnz, k)
         peak, peak_src = peaks()
         achieved = abytes / (ms_avg * 1e-3) / 1e9
-        gathered = (world - 1) * part.stride * k * 4
+        gathered = int(halo_rows) * k * 4
         print(json.dumps({
             "metric": METRIC, "value": flops / (ms_avg * 1e-3) / 1e9, "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_avg, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{name} SpMM C=A·B, k={k}, 1-D row partition by nnz over {world} GPUs, "
-                                   "NCCL all-gather of B overlapped with the local-column block",
-                       "n": n, "nnz": nnz, "k": k,
+                                   + ("halo rows pulled over NVLink peer memory (gcnb_pull_rows)"
+                                      if args.exchange == "pull" else "NCCL all-gather of B")
+                                   + " overlapped with the local-column block",
+                       "n": n, "nnz": nnz, "k": k, "exchange": args.exchange,
                        "local_nnz_frac": stats[0].item() / max(nnz, 1),
-                       "allgather_bytes_received_per_rank": gathered,
+                       "exchange_bytes_received_per_rank_max": gathered,
                        "l2": "operands >> L2; no flush needed"},
-            "gpu_launches": 2 * args.steps, "ms_median": ms_med, "ms_min": ms_min,
+            "phase_ms_alone": {"local_block_spmm": ph_local, "exchange": ph_exch, "remote_block_spmm": ph_remote,
+                               "note": "median of 5, each phase run alone, max over ranks; the step overlaps the first two"},
+            "gpu_launches": (3 if args.exchange == "pull" else 2) * args.steps, "ms_median": ms_med, "ms_min": ms_min,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak * world, "unit": "GB/s",
                          "frac": achieved / (peak * world), "traffic": None, "peak_source": peak_src,
                          "note": "aggregate: algorithmic bytes of the whole SpMM over N x per-GPU HBM peak; "

@@ -229,7 +229,13 @@ static void launch_stream_cfg(const LaunchArgs& a, int64_t gs, unsigned ytiles) 
 template <typename TB, int VEC, int NV>
 static int launch_stream(const LaunchArgs& a, int64_t gs, unsigned ytiles) {
   static const int cfg = getenv("GCNB_STREAM_CFG") ? atoi(getenv("GCNB_STREAM_CFG")) : 0;
-  constexpr int F = NV * VEC;   // floats per lane per gathered row
+  constexpr int F = NV * VEC;                        // accumulator registers per lane
+  constexpr int R = F * (int)sizeof(TB) / 4;         // registers per ring slot (raw gathered row)
+  // measured on the products-shaped graph (profiles/r01_e_stream_cfg_sweep.jsonl, r01_j_*): what
+  // counts is resident warps x slots in flight.  fp32 k=100 (F=4,R=4): U=4 at 64 regs / 32 warps per
+  // SM beats every other point; bf16 k=100 (F=4,R=2): U=4 at 48 regs / 40 warps.  bf16 with 16-byte
+  // loads (F=8,R=4) was 1.6x slower with the U=2 ring the fp32 F=8 case needs, so the ring depth
+  // follows R, not F.
   if constexpr (F <= 4) {
     switch (cfg) {
       case 1: launch_stream_cfg<TB, VEC, NV, 4, 10>(a, gs, ytiles); break;   // 48 regs, 40 warps/SM
@@ -238,24 +244,27 @@ static int launch_stream(const LaunchArgs& a, int64_t gs, unsigned ytiles) {
       case 4: launch_stream_cfg<TB, VEC, NV, 2, 12>(a, gs, ytiles); break;
       case 5: launch_stream_cfg<TB, VEC, NV, 8, 6>(a, gs, ytiles); break;
       default:
-        // measured on the products-shaped graph (profiles/r01_e_stream_cfg_sweep.jsonl): fp32 slots
-        // (4 registers) are fastest at 64 regs / 32 warps per SM, bf16 slots (2 registers) fit 48
-        // regs and gain from 40 warps per SM
-        if constexpr (sizeof(TB) == 2) launch_stream_cfg<TB, VEC, NV, 4, 10>(a, gs, ytiles);
+        if constexpr (R <= 2) launch_stream_cfg<TB, VEC, NV, 4, 10>(a, gs, ytiles);
         else launch_stream_cfg<TB, VEC, NV, 4, 8>(a, gs, ytiles);
         break;
     }
   } else if constexpr (F <= 8) {
     switch (cfg) {
       case 1: launch_stream_cfg<TB, VEC, NV, 4, 6>(a, gs, ytiles); break;
-      case 2: launch_stream_cfg<TB, VEC, NV, 4, 5>(a, gs, ytiles); break;
-      default: launch_stream_cfg<TB, VEC, NV, 2, 8>(a, gs, ytiles); break;
+      case 2: launch_stream_cfg<TB, VEC, NV, 2, 8>(a, gs, ytiles); break;
+      default:
+        if constexpr (R <= 4) launch_stream_cfg<TB, VEC, NV, 4, 8>(a, gs, ytiles);   // bf16: 16 ring + 8 acc
+        else launch_stream_cfg<TB, VEC, NV, 2, 8>(a, gs, ytiles);
+        break;
     }
   } else {
     switch (cfg) {
       case 1: launch_stream_cfg<TB, VEC, NV, 2, 6>(a, gs, ytiles); break;
       case 2: launch_stream_cfg<TB, VEC, NV, 1, 8>(a, gs, ytiles); break;
-      default: launch_stream_cfg<TB, VEC, NV, 2, 5>(a, gs, ytiles); break;
+      default:
+        if constexpr (R <= 8) launch_stream_cfg<TB, VEC, NV, 2, 8>(a, gs, ytiles);   // bf16: 16 ring + 16 acc
+        else launch_stream_cfg<TB, VEC, NV, 2, 5>(a, gs, ytiles);
+        break;
     }
   }
   return GCNB_OK;
@@ -364,7 +373,13 @@ static int spmm_dispatch(const Matrix& M, const void* B, int b_dtype, int64_t ld
     else
       rc = launch_vec<float, 1, 4>(a);
   } else {
-    if (k % 8 == 0 && ldb % 8 == 0 && ldc % 4 == 0 && aligned(B, 16) && aligned(C, 16))
+    // wide rows (stream class): 8-byte loads over up to 32 lanes measured 1.6x faster than 16-byte
+    // loads over half as many lanes (products-shaped, k = 128: 3.1 vs 4.9 ms, profiles/r01_j_*), so
+    // 16-byte loads are kept for the narrow lane-group kernel only
+    const bool v4ok = k % 4 == 0 && ldb % 4 == 0 && ldc % 4 == 0 && aligned(B, 8) && aligned(C, 16);
+    if (v4ok && k > 64)
+      rc = launch_vec<__nv_bfloat16, 4, 4>(a);
+    else if (k % 8 == 0 && ldb % 8 == 0 && ldc % 4 == 0 && aligned(B, 16) && aligned(C, 16))
       rc = launch_vec<__nv_bfloat16, 8, 2>(a);
     else if (k % 4 == 0 && ldb % 4 == 0 && ldc % 4 == 0 && aligned(B, 8) && aligned(C, 16))
       rc = launch_vec<__nv_bfloat16, 4, 4>(a);

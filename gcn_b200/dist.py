@@ -14,9 +14,21 @@ operation on the transposed blocks (``dB_p = Σ_q Â_qpᵀ dC_q`` = row block p 
 gathered dC), so it also costs one all-gather and no reduce-scatter; for a symmetric Â the
 transposed blocks are the forward blocks.
 
-Column ids of the remote part are remapped once, on the host, into the padded layout
-``q * stride + (col - bounds[q])`` that ``all_gather_into_tensor`` produces (equal-sized slots of
-``stride = max block rows``), so no compaction copy is needed after the gather.
+Two ways of bringing the remote rows in (``exchange=``):
+
+``"allgather"``  NCCL ``all_gather_into_tensor`` of the padded blocks.  Column ids of the remote part
+    are remapped once, on the host, into the padded layout ``q * stride + (col - bounds[q])`` that
+    the collective produces (equal-sized slots of ``stride = max block rows``), so no compaction
+    copy is needed after the gather.
+``"pull"``  our own kernel over NVLink peer memory (``gcnb_pull_rows``, gcn_b200/csrc/peer.cu).  Every
+    rank publishes its block in an exchange buffer the peers have mapped through CUDA IPC; the
+    *halo* — the distinct remote rows this rank's non-zeros touch, listed once at plan time and
+    sorted by (owner, row) — is read straight out of the owners' HBM into a compact buffer, and the
+    remote part's column ids index that buffer.  Only rows that are needed cross NVLink, once.
+    Ordering between ranks: a one-element all-reduce on the exchange stream after the block is
+    published (so every peer's block is complete before anybody pulls); the exchange buffer is
+    double-buffered, which makes that same all-reduce of the NEXT exchange the proof that all
+    pulls of this one have finished before its slot is overwritten.
 """
 from __future__ import annotations
 
@@ -76,11 +88,86 @@ def split_local_remote(rowptr, col, val, bounds, rank: int):
     return local, remote, stride
 
 
+def compact_halo(remote, bounds, stride: int):
+    """Re-index the remote part of a row block by its halo.
+
+    `remote` is the CSR returned by :func:`split_local_remote` (column ids in the padded layout
+    ``owner * stride + row_in_owner``).  Returns (csr, halo_part, halo_row): the same CSR with
+    column ids replaced by positions in the sorted list of DISTINCT remote rows, and that list as
+    (owner rank, row inside the owner's block) int32 arrays — sorted by owner, then row, which is
+    also ascending global id, so columns stay ascending within a row."""
+    rp, col, val = remote
+    uniq, inv = np.unique(col.astype(np.int64), return_inverse=True)
+    halo_part = (uniq // max(stride, 1)).astype(np.int32)
+    halo_row = (uniq - halo_part.astype(np.int64) * stride).astype(np.int32)
+    return (rp, inv.astype(np.int32), val), halo_part, halo_row
+
+
+class _PeerExchange:
+    """Double-buffered exchange buffer of one rank for one (row width, dtype), mapped on every peer.
+
+    Collective to construct (handles travel by ``all_gather_object``)."""
+
+    def __init__(self, rows: int, k: int, device, group):
+        import ctypes
+        from . import _ffi
+        self._ffi, self._ct = _ffi, ctypes
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self.device, self.rows, self.k = device, int(rows), int(k)
+        self.slot_bytes = ((self.rows * self.k * 4 + 255) // 256) * 256
+        ptr = ctypes.c_void_p()
+        handle = (ctypes.c_ubyte * 64)()
+        _ffi.call("gcnb_peer_alloc", device.index, 2 * self.slot_bytes, ctypes.byref(ptr), handle)
+        self.own_ptr = ptr.value
+        handles = [None] * self.world
+        dist.all_gather_object(handles, bytes(handle), group=group)
+        self.base = []          # device pointer of every rank's buffer in THIS process
+        self._opened = []
+        for q, h in enumerate(handles):
+            if q == self.rank:
+                self.base.append(self.own_ptr)
+                continue
+            p = ctypes.c_void_p()
+            _ffi.call("gcnb_peer_open", device.index, (ctypes.c_ubyte * 64).from_buffer_copy(h), ctypes.byref(p))
+            self.base.append(p.value)
+            self._opened.append(p.value)
+        self.own = [self._wrap(self.own_ptr + s * self.slot_bytes) for s in (0, 1)]
+        self.turn = 0
+
+    def _wrap(self, ptr):
+        class _Raw:   # CUDA array interface view of the raw allocation (the library owns the memory)
+            pass
+        raw = _Raw()
+        raw.__cuda_array_interface__ = {"shape": (self.rows, self.k), "typestr": "<f4", "data": (ptr, False),
+                                        "version": 2, "strides": None}
+        t = torch.as_tensor(raw, device=self.device)
+        assert t.data_ptr() == ptr
+        return t
+
+    def bases(self, slot: int):
+        arr = (self._ct.c_void_p * self.world)(*[b + slot * self.slot_bytes for b in self.base])
+        return arr
+
+    def close(self):
+        for p in self._opened:
+            self._ffi.lib.gcnb_peer_close(self.device.index, self._ct.c_void_p(p))
+        self._opened = []
+        if self.own_ptr:
+            self._ffi.lib.gcnb_peer_free(self.device.index, self._ct.c_void_p(self.own_ptr))
+            self.own_ptr = None
+
+
 class PartitionedSpMM:
     """Row block `rank` of Â (and of Âᵀ unless symmetric) prepared for the gathered SpMM."""
 
     def __init__(self, rowptr, col, val, n: int, group=None, device=None, bounds=None,
-                 symmetric: bool | None = None):
+                 symmetric: bool | None = None, exchange: str = "allgather"):
+        if exchange not in ("allgather", "pull"):
+            raise ValueError("exchange must be 'allgather' or 'pull'")
+        self.exchange = exchange
+        self._exchanges = {}     # k -> _PeerExchange
+        self._halo_bufs = {}     # (id(blocks), k) -> compact halo rows
+        self._flag = None
         self.group = group
         self.rank = dist.get_rank(group)
         self.world = dist.get_world_size(group)
@@ -101,17 +188,28 @@ class PartitionedSpMM:
         else:
             t_rowptr, t_col, t_val = _transpose(rowptr, col, val, self.n)
             self.bwd = self._make_blocks(t_rowptr, t_col, t_val)
-        self._side = torch.cuda.Stream(self.device) if self.device.type == "cuda" else None
+        # exchange stream: high priority, so that its (few, short) CTAs are scheduled between the
+        # CTAs of the local-block SpMM that fills the machine at the same time
+        self._side = torch.cuda.Stream(self.device, priority=-1) if self.device.type == "cuda" else None
 
     def _make_blocks(self, rowptr, col, val):
         local, remote, stride = split_local_remote(rowptr, col, val, self.bounds, self.rank)
         self.stride = stride
         blocks = {"local_csr": local, "remote_csr": remote}
+        n_remote_cols = self.world * stride
+        if self.exchange == "pull":
+            remote, halo_part, halo_row = compact_halo(remote, self.bounds, stride)
+            blocks["remote_csr"] = remote
+            blocks["halo_part_np"], blocks["halo_row_np"] = halo_part, halo_row
+            blocks["halo_part"] = torch.from_numpy(halo_part).to(self.device)
+            blocks["halo_row"] = torch.from_numpy(halo_row).to(self.device)
+            n_remote_cols = max(len(halo_row), 1)
+        blocks["n_remote_cols"] = n_remote_cols
         if self.device.type == "cuda":
             # forward-only plans: the transposed blocks are separate plans (self.bwd)
             blocks["local"] = ops.SpmmPlan(*local, (self.m_local, self.m_local), device=self.device,
                                            need_transpose=False)
-            blocks["remote"] = ops.SpmmPlan(*remote, (self.m_local, self.world * stride),
+            blocks["remote"] = ops.SpmmPlan(*remote, (self.m_local, n_remote_cols),
                                             device=self.device, need_transpose=False)
         return blocks
 
@@ -132,21 +230,80 @@ class PartitionedSpMM:
         dist.all_gather_into_tensor(full, padded.contiguous(), group=self.group)
         return full
 
+    # ---- "pull" exchange ------------------------------------------------------------------------
+    def _exchange_for(self, k: int):
+        ex = self._exchanges.get(k)
+        if ex is None:   # collective: every rank reaches its first SpMM of width k together
+            ex = self._exchanges[k] = _PeerExchange(self.stride, k, self.device, self.group)
+        return ex
+
+    def _publish(self, ex, B_local):
+        """Copy the local block into the free slot of the exchange buffer; returns the slot."""
+        slot = ex.turn
+        ex.turn ^= 1
+        ex.own[slot][: self.m_local].copy_(B_local)
+        return slot
+
+    def _rank_barrier(self):
+        """Stream-ordered rendezvous of all ranks (a one-element all-reduce on the current stream)."""
+        if self._flag is None:
+            self._flag = torch.zeros(1, dtype=torch.float32, device=self.device)
+        dist.all_reduce(self._flag, group=self.group)
+
+    def _pull(self, blocks, ex, slot, k):
+        """The halo rows of `blocks`, compact, read out of the owners' exchange buffers."""
+        import ctypes
+        from . import _ffi
+        n_halo = blocks["halo_row"].numel()
+        key = (id(blocks), k)
+        halo = self._halo_bufs.get(key)
+        if halo is None:
+            halo = self._halo_bufs[key] = torch.empty((blocks["n_remote_cols"], k), dtype=torch.float32,
+                                                      device=self.device)
+        if n_halo:
+            _ffi.call("gcnb_pull_rows", ex.bases(slot), self.world, k * 4,
+                      ctypes.c_void_p(blocks["halo_part"].data_ptr()),
+                      ctypes.c_void_p(blocks["halo_row"].data_ptr()), ctypes.c_void_p(halo.data_ptr()),
+                      k * 4, n_halo, k * 4,
+                      ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream))
+        return halo
+
+    def _exchange(self, blocks, B_local, pre=None):
+        """Remote rows of the operand in the layout the remote block's columns index.  `pre` is what
+        _prepare returned on the compute stream (the published slot in pull mode)."""
+        if self.exchange == "allgather":
+            return self._gathered(blocks, B_local)
+        ex, slot = pre
+        self._rank_barrier()
+        return self._pull(blocks, ex, slot, B_local.shape[1])
+
+    def _prepare(self, B_local):
+        if self.exchange == "allgather":
+            return None
+        ex = self._exchange_for(B_local.shape[1])
+        return ex, self._publish(ex, B_local)
+
+    def close(self):
+        for ex in self._exchanges.values():
+            ex.close()
+        self._exchanges = {}
+
     def _apply(self, blocks, B_local: torch.Tensor) -> torch.Tensor:
         if B_local.shape[0] != self.m_local:
             raise ValueError(f"rank {self.rank} owns {self.m_local} rows, operand has {B_local.shape[0]}")
         B_local = B_local.contiguous()
         out = torch.empty((self.m_local, B_local.shape[1]), dtype=torch.float32, device=B_local.device)
+        pre = self._prepare(B_local)
         if self._side is not None:
             cur = torch.cuda.current_stream(self.device)
             self._side.wait_stream(cur)
             with torch.cuda.stream(self._side):
-                full = self._gathered(blocks, B_local)
+                full = self._exchange(blocks, B_local, pre)
             self._mul_local(blocks, B_local, out)          # overlaps the all-gather
             cur.wait_stream(self._side)
             full.record_stream(cur)
         else:
-            full = self._gathered(blocks, B_local)
+            full = self._exchange(blocks, B_local, pre)
             self._mul_local(blocks, B_local, out)
         self._mul_remote_accumulate(blocks, full, out)
         return out

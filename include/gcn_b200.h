@@ -112,6 +112,27 @@ int gcnb_xw(const float* X, int64_t ldx, int trans_x, const float* W, int64_t ld
             int precision, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Multi-GPU exchange over NVLink peer memory (the reference is single-GPU).
+ * One process per GPU.  Every rank allocates an exchange buffer (gcnb_peer_alloc), sends the
+ * 64-byte handle to its peers by any host channel (torch.distributed), and maps theirs
+ * (gcnb_peer_open, CUDA IPC with lazily enabled peer access).  gcnb_pull_rows then copies the
+ * halo rows a rank needs straight out of the owners' HBM:
+ *     out[i, :] = bases[part[i]][row[i], :]          (row_bytes bytes per row)
+ * bases: HOST array of n_parts device pointers (own buffer or opened peers; entries never read may
+ * be null); part,row: DEVICE int32[n_rows]; out: DEVICE.  Ordering between ranks (a block must be
+ * written before a peer pulls it, and pulled before it is overwritten) is the caller's: see
+ * gcn_b200/dist.py.
+ * ------------------------------------------------------------------------------------------- */
+#define GCNB_IPC_HANDLE_BYTES 64
+int gcnb_peer_alloc(int device, int64_t bytes, void** ptr_out, unsigned char* handle_out);
+int gcnb_peer_free(int device, void* ptr);
+int gcnb_peer_open(int device, const unsigned char* handle, void** ptr_out);
+int gcnb_peer_close(int device, void* ptr);
+int gcnb_pull_rows(const void* const* bases, int n_parts, int64_t src_pitch_bytes,
+                   const int32_t* part, const int32_t* row, void* out, int64_t out_pitch_bytes,
+                   int64_t n_rows, int64_t row_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Host graph preprocessing (bit-exact with the reference).  All arrays HOST memory.
  * rank_out[old] = new, the reference's order_* convention (order_rcm.cu:28-31).
  * ------------------------------------------------------------------------------------------- */

@@ -71,7 +71,50 @@ class _OraclePart(gdist.PartitionedSpMM):
         out.add_(torch.from_numpy(SO.spmm_f32(rp, ci, va, B_gathered.shape[0], B_gathered.numpy())))
 
 
-def _worker(rank, world, port, symmetric, q):
+class _OraclePartPull(_OraclePart):
+    """Pull mode on CPU: the peer-memory read is replaced by an all-gather + the halo index (what
+    gcnb_pull_rows reads out of the owners' buffers), everything else is the product's logic."""
+
+    def _exchange_for(self, k):
+        return None
+
+    def _publish(self, ex, B_local):
+        self._published = B_local
+        return 0
+
+    def _pull(self, blocks, ex, slot, k):
+        padded = torch.zeros((self.stride, k))
+        padded[: self.m_local] = self._published
+        full = torch.empty((self.world * self.stride, k))
+        dist.all_gather_into_tensor(full, padded, group=self.group)
+        idx = blocks["halo_part"].long() * self.stride + blocks["halo_row"].long()
+        return full[idx] if idx.numel() else torch.zeros((1, k))
+
+
+def test_compact_halo_reindexes_remote_block():
+    A = random_normalized_graph(211, 1500, 5, "skew")
+    n = A.shape[0]
+    B = np.random.default_rng(2).standard_normal((n, 3)).astype(np.float32)
+    parts = 4
+    bounds = gdist.nnz_balanced_bounds(A.indptr, parts)
+    for p in range(parts):
+        _, remote, stride = gdist.split_local_remote(A.indptr, A.indices, A.data, bounds, p)
+        csr, hp, hr = gdist.compact_halo(remote, bounds, stride)
+        assert hp.dtype == np.int32 and hr.dtype == np.int32 and len(hp) == len(hr)
+        gid = bounds[hp] + hr                       # global ids of the halo rows
+        assert np.all(np.diff(gid) > 0)             # distinct, ascending => sorted by (owner, row)
+        assert not np.any((gid >= bounds[p]) & (gid < bounds[p + 1]))   # nothing local in the halo
+        assert len(gid) == len(np.unique(remote[1])) and np.all(hr < np.diff(bounds)[hp])
+        m_p = bounds[p + 1] - bounds[p]
+        padded = np.zeros((parts * stride, 3), dtype=np.float32)
+        for q in range(parts):
+            padded[q * stride: q * stride + bounds[q + 1] - bounds[q]] = B[bounds[q]:bounds[q + 1]]
+        want = SO.spmm_f64(*remote, parts * stride, padded)
+        got = SO.spmm_f64(*csr, max(len(gid), 1), B[gid] if len(gid) else np.zeros((1, 3), np.float32))
+        assert want.shape[0] == m_p and np.array_equal(got, want)
+
+
+def _worker(rank, world, port, symmetric, q, exchange="allgather"):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -85,12 +128,16 @@ def _worker(rank, world, port, symmetric, q):
         rng = np.random.default_rng(1)
         B = rng.standard_normal((n, 6)).astype(np.float32)
         G = rng.standard_normal((n, 6)).astype(np.float32)
-        part = _OraclePart(A.indptr, A.indices, A.data, n, device="cpu")
+        cls = _OraclePartPull if exchange == "pull" else _OraclePart
+        part = cls(A.indptr, A.indices, A.data, n, device="cpu", exchange=exchange)
         assert part.symmetric == symmetric
         lo, hi = part.lo, part.hi
         Bl = torch.from_numpy(B[lo:hi].copy()).requires_grad_(True)
         out = gdist.spmm(part, Bl)
         out.backward(torch.from_numpy(G[lo:hi].copy()))
+        if exchange == "pull":   # a second round through the same buffers
+            out2 = gdist.spmm(part, Bl.detach())
+            assert torch.equal(out2, out.detach())
         fwd = rel_err(out.detach().numpy(), SO.spmm_f64(A.indptr, A.indices, A.data, n, B)[lo:hi])
         bwd = rel_err(Bl.grad.numpy(), SO.spmm_t_f64(A.indptr, A.indices, A.data, n, G)[lo:hi])
         # replicated-weight gradient all-reduce
@@ -104,13 +151,14 @@ def _worker(rank, world, port, symmetric, q):
         dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("exchange", ["allgather", "pull"])
 @pytest.mark.parametrize("symmetric", [True, False])
-def test_two_rank_gathered_spmm_gloo(symmetric):
+def test_two_rank_gathered_spmm_gloo(symmetric, exchange):
     world = 2
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, symmetric, q)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, symmetric, q, exchange)) for r in range(world)]
     for p in procs:
         p.start()
     res = [q.get(timeout=120) for _ in range(world)]

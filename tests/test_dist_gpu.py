@@ -1,0 +1,117 @@
+"""Multi-GPU exchange on a real device.  The driver's GPU box for `pytest -m gpu` has ONE B200, so the
+two ranks of the partitioned SpMM share cuda:0: CUDA IPC between two processes works the same on
+one device, which exercises gcnb_peer_alloc/open, gcnb_pull_rows and the whole pull-mode path
+(halo index, double-buffered exchange slots, accumulate epilogue) with the real kernels.  NCCL
+refuses two ranks on one GPU, so the host channel here is gloo and the rank barrier is a
+synchronise + gloo barrier; bench.py --gpus N runs the same code over NCCL on N GPUs."""
+import ctypes
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from conftest import random_normalized_graph, rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+def test_pull_rows_single_process():
+    from gcn_b200 import _ffi
+    dev = torch.device("cuda", 0)
+    rng = np.random.default_rng(3)
+    for k in (100, 25, 7, 256):     # 16-byte, 4-byte aligned rows
+        n_src, n_out = 1000, 777
+        bufs = [torch.from_numpy(rng.standard_normal((n_src, k)).astype(np.float32)).to(dev) for _ in range(3)]
+        part = rng.integers(0, 3, n_out).astype(np.int32)
+        row = rng.integers(0, n_src, n_out).astype(np.int32)
+        out = torch.full((n_out, k), float("nan"), device=dev)
+        bases = (ctypes.c_void_p * 3)(*[b.data_ptr() for b in bufs])
+        part_d, row_d = torch.from_numpy(part).to(dev), torch.from_numpy(row).to(dev)   # keep alive
+        _ffi.call("gcnb_pull_rows", bases, 3, k * 4, ctypes.c_void_p(part_d.data_ptr()),
+                  ctypes.c_void_p(row_d.data_ptr()), ctypes.c_void_p(out.data_ptr()),
+                  k * 4, n_out, k * 4, ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream))
+        torch.cuda.synchronize()
+        want = np.stack([bufs[p][r].cpu().numpy() for p, r in zip(part, row)])
+        assert np.array_equal(out.cpu().numpy(), want)     # a copy: bit-exact
+    # argument errors are reported, not crashed on
+    assert _ffi.lib.gcnb_pull_rows(None, 3, 4, None, None, None, 4, 5, 4, None) == -1
+    assert _ffi.lib.gcnb_pull_rows(bases, 99, 4, None, None, None, 4, 0, 4, None) == 0   # empty: no-op
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, symmetric, exchange, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import scipy.sparse as sp
+        from gcn_b200 import dist as gdist
+        from oracle import spmm_oracle as SO
+
+        class Part(gdist.PartitionedSpMM):
+            def _rank_barrier(self):          # two ranks on one GPU: no NCCL; order them on the host
+                torch.cuda.synchronize()
+                dist.barrier()
+
+        dev = torch.device("cuda", 0)
+        torch.cuda.set_device(dev)
+        A = random_normalized_graph(1500, 20000, 11, "skew")
+        if not symmetric:
+            A = sp.triu(A).tocsr()
+            A.sort_indices()
+        n = A.shape[0]
+        rng = np.random.default_rng(1)
+        errs = []
+        part = Part(A.indptr, A.indices, A.data, n, device=dev, exchange=exchange)
+        for k in (100, 16):
+            B = rng.standard_normal((n, k)).astype(np.float32)
+            G = rng.standard_normal((n, k)).astype(np.float32)
+            lo, hi = part.lo, part.hi
+            for _ in range(3):      # several rounds through the double-buffered slots
+                Bl = torch.from_numpy(B[lo:hi].copy()).to(dev).requires_grad_(True)
+                out = gdist.spmm(part, Bl)
+                out.backward(torch.from_numpy(G[lo:hi].copy()).to(dev))
+                torch.cuda.synchronize()
+                errs.append(rel_err(out.detach().cpu().numpy(),
+                                    SO.spmm_f64(A.indptr, A.indices, A.data, n, B)[lo:hi]))
+                errs.append(rel_err(Bl.grad.cpu().numpy(),
+                                    SO.spmm_t_f64(A.indptr, A.indices, A.data, n, G)[lo:hi]))
+                B = B + 1.0     # new contents every round: a stale slot would show
+                G = G - 0.5
+        torch.cuda.synchronize()
+        dist.barrier()
+        part.close()
+        q.put((rank, max(errs)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("exchange", ["pull", "allgather"])
+@pytest.mark.parametrize("symmetric", [True, False])
+def test_two_ranks_one_gpu(symmetric, exchange):
+    if exchange == "allgather":
+        pytest.skip("all_gather_into_tensor needs NCCL (one rank per GPU); covered by bench.py --gpus N")
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, symmetric, exchange, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=300) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, err in res:
+        assert err < 1e-5, (rank, err)     # north_star: 1e-5 relative, fp32
