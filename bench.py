@@ -411,6 +411,12 @@ def run_multi(args):
     remote_nnz = int(part.fwd["remote_csr"][0][-1])
     g = torch.Generator(device=device).manual_seed(15 + rank)
     B = torch.randn(part.m_local, k, device=device, generator=g)
+    if args.exchange == "pull":
+        # the operand is resident where its producer would have written it: the exchange slot
+        # (gcn_b200.dist.PartitionedGCN does that with the X·W product)
+        slot = part.next_operand(k)
+        slot.copy_(B)
+        B = slot
 
     def barrier():
         dist.barrier(device_ids=[local])

@@ -6,7 +6,10 @@
 // buffer that the peers map through CUDA IPC, and pulls exactly its halo rows out of the owners'
 // HBM with 128-bit P2P loads (gcnb_pull_rows): only rows that are needed cross NVLink, once each,
 // and land compacted in the index space the remote block's column ids use.
+#include <stdlib.h>
 #include <string.h>
+
+#include <algorithm>
 
 #include "common.h"
 
@@ -21,29 +24,38 @@ struct PeerBases {
 };
 
 // out[i, 0:row_bytes) = bases[part[i]][row[i] * src_pitch .. + row_bytes)
+// Persistent, deliberately small grid (a couple of CTAs per SM, grid-stride over the halo): the pull
+// is bound by NVLink, not by SM resources, and it runs at the same time as the local-block SpMM, which
+// fills the register file; a grid sized by the halo would occupy every SM with warps that only wait on
+// the link and serialise the two (measured on 2 GPUs, products-shaped: step 3.05 ms with a halo-sized
+// grid, 2.75 / 2.69 / 2.45 ms with 4 / 2 / 1 CTAs per SM, profiles/r01_n_*; default 1).
+// In flight: warps x kPullRowsPerWarp rows x row_bytes (148 x 8 x 4 x 400 B = 1.9 MB), about the
+// ~2 us x 900 GB/s the link needs.
 template <typename V>
 __global__ void __launch_bounds__(kPullWarps * 32)
 pull_rows_kernel(PeerBases bases, const int32_t* __restrict__ part, const int32_t* __restrict__ row,
                  char* __restrict__ out, int64_t src_pitch, int64_t out_pitch, int64_t n_rows,
                  int vecs_per_row) {
   const int lane = threadIdx.x & 31;
-  const int64_t w = (int64_t)blockIdx.x * kPullWarps + (threadIdx.x >> 5);
-  const int64_t r0 = w * kPullRowsPerWarp;
-  if (r0 >= n_rows) return;
-  const V* src[kPullRowsPerWarp];
-  V* dst[kPullRowsPerWarp];
+  const int64_t n_warps = (int64_t)gridDim.x * kPullWarps;
+  for (int64_t w = (int64_t)blockIdx.x * kPullWarps + (threadIdx.x >> 5); w * kPullRowsPerWarp < n_rows;
+       w += n_warps) {
+    const int64_t r0 = w * kPullRowsPerWarp;
+    const V* src[kPullRowsPerWarp];
+    V* dst[kPullRowsPerWarp];
 #pragma unroll
-  for (int j = 0; j < kPullRowsPerWarp; ++j) {
-    const int64_t r = min(r0 + j, n_rows - 1);   // clamp: duplicates rewrite the same bytes
-    src[j] = reinterpret_cast<const V*>(bases.p[__ldg(part + r)] + (int64_t)__ldg(row + r) * src_pitch);
-    dst[j] = reinterpret_cast<V*>(out + r * out_pitch);
-  }
-  for (int i = lane; i < vecs_per_row; i += 32) {
-    V v[kPullRowsPerWarp];
+    for (int j = 0; j < kPullRowsPerWarp; ++j) {
+      const int64_t r = min(r0 + j, n_rows - 1);   // clamp: duplicates rewrite the same bytes
+      src[j] = reinterpret_cast<const V*>(bases.p[__ldg(part + r)] + (int64_t)__ldg(row + r) * src_pitch);
+      dst[j] = reinterpret_cast<V*>(out + r * out_pitch);
+    }
+    for (int i = lane; i < vecs_per_row; i += 32) {
+      V v[kPullRowsPerWarp];
 #pragma unroll
-    for (int j = 0; j < kPullRowsPerWarp; ++j) v[j] = src[j][i];   // peer memory: plain (coherent) loads
+      for (int j = 0; j < kPullRowsPerWarp; ++j) v[j] = src[j][i];   // peer memory: plain (coherent) loads
 #pragma unroll
-    for (int j = 0; j < kPullRowsPerWarp; ++j) dst[j][i] = v[j];
+      for (int j = 0; j < kPullRowsPerWarp; ++j) dst[j][i] = v[j];
+    }
   }
 }
 
@@ -129,8 +141,9 @@ int gcnb_pull_rows(const void* const* bases, int n_parts, int64_t src_pitch_byte
     align |= (uintptr_t)pb.p[q];   // a part this rank never reads may be null
   }
   const int64_t warps = (n_rows + kPullRowsPerWarp - 1) / kPullRowsPerWarp;
-  const int64_t blocks = (warps + kPullWarps - 1) / kPullWarps;
-  GCNB_REQUIRE(blocks <= 0x7fffffffLL, "too many rows for one grid");
+  static const int ctas_per_sm = getenv("GCNB_PULL_CTAS") ? atoi(getenv("GCNB_PULL_CTAS")) : 1;
+  const int64_t blocks = std::min<int64_t>((warps + kPullWarps - 1) / kPullWarps,
+                                           (int64_t)std::max(1, sm_count(dev)) * std::max(1, ctas_per_sm));
   cudaStream_t s = (cudaStream_t)stream;
   if (align % 16 == 0)
     pull_rows_kernel<uint4><<<(unsigned)blocks, kPullWarps * 32, 0, s>>>(

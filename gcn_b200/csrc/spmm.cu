@@ -285,6 +285,9 @@ static int launch_one(const LaunchArgs& a) {
       const int64_t gw = (M.m + kWarpRowWarps - 1) / kWarpRowWarps;
       if (gw > 0x7fffffffLL || a.ldb * (int64_t)sizeof(TB) > 0xffffffffLL)
         return set_error(GCNB_ERR_UNSUPPORTED, "matrix too large for one grid");
+      // default 3 = stream class.  (A warp per row with the C load hoisted was tried for the
+      // accumulating remote-column block of the row-partitioned SpMM, ~2.6 non-zeros per row:
+      // 0.80 ms against the stream kernel's 0.60 ms on 2 GPUs, profiles/r01_m_*.)
       static const int variant = getenv("GCNB_SPMM_VARIANT") ? atoi(getenv("GCNB_SPMM_VARIANT")) : 3;
       if (variant == 3) {
         // stream class covers every row, long ones included: one launch (+ the split-row reduction)

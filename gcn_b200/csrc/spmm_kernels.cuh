@@ -58,6 +58,11 @@ struct VecLoad<float, 4> {
     const float4 v = __ldg(reinterpret_cast<const float4*>(p));
     o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w;
   }
+  // coherent load (C in accumulate mode was written by the previous kernel, not read-only data)
+  static __device__ __forceinline__ void load_plain(const float* p, float (&o)[4]) {
+    const float4 v = *reinterpret_cast<const float4*>(p);
+    o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w;
+  }
 };
 template <>
 struct VecLoad<float, 2> {
@@ -65,10 +70,15 @@ struct VecLoad<float, 2> {
     const float2 v = __ldg(reinterpret_cast<const float2*>(p));
     o[0] = v.x; o[1] = v.y;
   }
+  static __device__ __forceinline__ void load_plain(const float* p, float (&o)[2]) {
+    const float2 v = *reinterpret_cast<const float2*>(p);
+    o[0] = v.x; o[1] = v.y;
+  }
 };
 template <>
 struct VecLoad<float, 1> {
   static __device__ __forceinline__ void load(const float* p, float (&o)[1]) { o[0] = __ldg(p); }
+  static __device__ __forceinline__ void load_plain(const float* p, float (&o)[1]) { o[0] = *p; }
 };
 
 __device__ __forceinline__ void bf16x2_to_f32(uint32_t w, float& lo, float& hi) {
@@ -168,6 +178,24 @@ __device__ __forceinline__ void store_vec(float* p, const float (&v)[VEC]) {
     __stcs(reinterpret_cast<float2*>(p), make_float2(v[0], v[1]));
   } else {
     __stcs(p, v[0]);
+  }
+}
+
+// existing C values in accumulate mode: coherent loads (written by the previous kernel), same vector
+// widths as store_vec
+template <int VEC>
+__device__ __forceinline__ void load_c(const float* p, float (&v)[VEC]) {
+  if constexpr (VEC % 4 == 0) {
+#pragma unroll
+    for (int i = 0; i < VEC; i += 4) {
+      const float4 q = *reinterpret_cast<const float4*>(p + i);
+      v[i] = q.x; v[i + 1] = q.y; v[i + 2] = q.z; v[i + 3] = q.w;
+    }
+  } else if constexpr (VEC == 2) {
+    const float2 q = *reinterpret_cast<const float2*>(p);
+    v[0] = q.x; v[1] = q.y;
+  } else {
+    v[0] = *p;
   }
 }
 
@@ -326,6 +354,7 @@ spmm_warp_row_kernel(const int32_t* __restrict__ rowptr, const int2* __restrict_
   const int beg = __ldg(rowptr + row);
   int len = __ldg(rowptr + row + 1) - beg;
   if (len >= long_thresh) return;   // the block class computes this row
+  if (len == 0 && epi == GCNB_EPI_ACCUM) return;   // C += 0: nothing to do
 
   bool cok[NV];
   int coff[NV];
@@ -336,11 +365,18 @@ spmm_warp_row_kernel(const int32_t* __restrict__ rowptr, const int2* __restrict_
   }
   // per-lane base: out-of-range lanes are parked on column 0 and never load
   const char* bl = reinterpret_cast<const char*>(B + (cok[0] ? coff[0] : 0));
+  // accumulate mode starts from the existing C row: that load depends on nothing but the row id, so
+  // it is issued first and arrives under the rowptr -> (col,val) -> feature-row chain
   float acc[NV][VEC];
 #pragma unroll
-  for (int t = 0; t < NV; ++t)
+  for (int t = 0; t < NV; ++t) {
+    if ((epi & GCNB_EPI_ACCUM) && cok[t]) {
+      load_c<VEC>(C + row * ldc + coff[t], acc[t]);
+    } else {
 #pragma unroll
-    for (int x = 0; x < VEC; ++x) acc[t][x] = 0.f;
+      for (int x = 0; x < VEC; ++x) acc[t][x] = 0.f;
+    }
+  }
 
   int2* slab = s_cv[warp];
   const int2* src = cv + beg;
@@ -442,10 +478,6 @@ spmm_warp_row_kernel(const int32_t* __restrict__ rowptr, const int2* __restrict_
   for (int t = 0; t < NV; ++t) {
     if (cok[t]) {
       float o[VEC];
-      if (epi & GCNB_EPI_ACCUM) {
-#pragma unroll
-        for (int x = 0; x < VEC; ++x) acc[t][x] += crow[coff[t] + x];
-      }
 #pragma unroll
       for (int x = 0; x < VEC; ++x) o[x] = epilogue(acc[t][x], bias, coff[t] + x, epi);
       store_vec<VEC>(crow + coff[t], o);
@@ -526,7 +558,26 @@ spmm_stream_kernel(const Seg* __restrict__ segs, int n_segs, const int32_t* __re
 #pragma unroll
     for (int x = 0; x < VEC; ++x) acc[t][x] = 0.f;
 
+  // accumulate mode (C += A·B, the remote-column block of the row-partitioned SpMM): every row end is a
+  // read-modify-write of a C row that nothing has touched yet, i.e. an HBM-latency load the store and
+  // the next row wait for.  The rows of a segment are consecutive, so their C lines are requested into
+  // L2 kPfAhead rows ahead (prefetch.global.L2: no register, no scoreboard), which turns that load into
+  // an L2 hit.
+  constexpr int kPfAhead = 8;
+  const bool pf = (epi_arg & GCNB_EPI_ACCUM) && !piece;
+  auto prefetch_c = [&](int r) {   // lanes 0..lines-1 each request one 128-byte line of C row r
+    if (r < r1 && lane * 32 < k) {
+      const float* p = C + (int64_t)r * ldc + lane * 32;
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+    }
+  };
+  if (pf) {
+#pragma unroll 1
+    for (int j = 0; j < kPfAhead; ++j) prefetch_c(row + j);
+  }
+
   auto flush = [&]() {   // write row `row`, move to the next one (warp-uniform)
+    if (pf) prefetch_c(row + kPfAhead);
     // (addresses are rebuilt from the kernel parameters here, off the hot path, to keep the gather
     // loop's register count down)
     float* crow = r1s < 0 ? partials + (int64_t)(-1 - r1s) * k : C + (int64_t)row * ldc;

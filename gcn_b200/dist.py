@@ -237,8 +237,23 @@ class PartitionedSpMM:
             ex = self._exchanges[k] = _PeerExchange(self.stride, k, self.device, self.group)
         return ex
 
+    def next_operand(self, k: int):
+        """Pull mode: a [m_local × k] float32 view of the free exchange slot for the producer of the
+        next operand (``gemm.xw(..., out=part.next_operand(k))``): an operand that already lives there
+        is published without a copy.  Collective on first use of a width.  None in all-gather mode."""
+        if self.exchange != "pull":
+            return None
+        ex = self._exchange_for(k)
+        slot = ex.turn
+        ex.turn ^= 1
+        return ex.own[slot][: self.m_local]
+
     def _publish(self, ex, B_local):
-        """Copy the local block into the free slot of the exchange buffer; returns the slot."""
+        """Make the local block visible to the peers; returns the slot it is in.  A block that was
+        produced in place (next_operand) is already there; anything else is copied into the free slot."""
+        for slot in (0, 1):
+            if B_local.data_ptr() == ex.own[slot].data_ptr() and B_local.stride(0) == ex.k:
+                return slot
         slot = ex.turn
         ex.turn ^= 1
         ex.own[slot][: self.m_local].copy_(B_local)
@@ -377,7 +392,8 @@ class PartitionedGCN(torch.nn.Module):
 
     def forward(self, x_local):
         from . import gemm
-        support = gemm.xw(x_local, self.gc1.weight)
+        nhid = self.gc1.weight.shape[1]
+        support = gemm.xw(x_local, self.gc1.weight, out=self.part.next_operand(nhid))   # straight into the exchange slot
         h = torch.relu(spmm(self.part, support) + self.gc1.bias)
         h = torch.nn.functional.dropout(h, self.dropout, training=self.training)
         s2 = spmm(self.part, h)

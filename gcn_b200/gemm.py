@@ -62,9 +62,11 @@ def gemm_raw(A: torch.Tensor, B: torch.Tensor, trans_a=False, trans_b=False, bia
 
 class _XW(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, X, W, bias, relu, precision):
+    def forward(ctx, X, W, bias, relu, precision, out=None):
+        if out is not None and relu:
+            raise ValueError("gemm.xw: `out` cannot be combined with relu (the result is kept for backward)")
         out = gemm_raw(X.detach(), W.detach(), bias=None if bias is None else bias.detach(),
-                       relu=relu, precision=precision)
+                       relu=relu, precision=precision, out=out)
         ctx.relu = relu
         ctx.precision = precision
         ctx.has_bias = bias is not None
@@ -84,10 +86,11 @@ class _XW(torch.autograd.Function):
             gW = gemm_raw(X.detach(), g, trans_a=True, precision=ctx.precision)      # Xᵀ · dS
         if ctx.has_bias and ctx.needs_input_grad[2]:
             gb = g.sum(dim=0)
-        return gX, gW, gb, None, None
+        return gX, gW, gb, None, None, None
 
 
 def xw(input: torch.Tensor, weight: torch.Tensor, bias=None, relu=False,
-       precision=PRECISION_3XTF32) -> torch.Tensor:
-    """``input @ weight (+ bias)(ReLU)`` with autograd, on tcgen05 tensor cores."""
-    return _XW.apply(input, weight, bias, bool(relu), int(precision))
+       precision=PRECISION_3XTF32, out=None) -> torch.Tensor:
+    """``input @ weight (+ bias)(ReLU)`` with autograd, on tcgen05 tensor cores.  `out`: write the
+    product into an existing float32 buffer (e.g. the exchange slot of the row-partitioned SpMM)."""
+    return _XW.apply(input, weight, bias, bool(relu), int(precision), out)

@@ -78,8 +78,13 @@ def _worker(rank, world, port, symmetric, exchange, q):
             B = rng.standard_normal((n, k)).astype(np.float32)
             G = rng.standard_normal((n, k)).astype(np.float32)
             lo, hi = part.lo, part.hi
-            for _ in range(3):      # several rounds through the double-buffered slots
-                Bl = torch.from_numpy(B[lo:hi].copy()).to(dev).requires_grad_(True)
+            for rnd in range(4):    # several rounds through the double-buffered slots
+                Bl = torch.from_numpy(B[lo:hi].copy()).to(dev)
+                if rnd >= 2 and exchange == "pull":   # operand produced in place in the exchange slot
+                    slot = part.next_operand(k)
+                    slot.copy_(Bl)
+                    Bl = slot.detach()
+                Bl.requires_grad_(True)
                 out = gdist.spmm(part, Bl)
                 out.backward(torch.from_numpy(G[lo:hi].copy()).to(dev))
                 torch.cuda.synchronize()
