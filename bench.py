@@ -88,47 +88,79 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
-    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons DURING the timed region (B200_PROFILING.md's clocks line), read
+    in-process through NVML every 10 ms.  (A first version spawned `nvidia-smi` every 100 ms from every
+    rank: with 8 ranks those processes took the driver lock in the middle of the timed steps and showed
+    up as multi-millisecond outlier steps.)  Falls back to one nvidia-smi query at the end."""
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
-    def __init__(self, index=0):
-        self.rows, self.stop, self.index = [], threading.Event(), index
+    def __init__(self, index=0, enabled=True):
+        self.index, self.enabled = index, enabled
+        self.sm, self.mx, self.bits, self.stop = [], None, 0, threading.Event()
+        self.nv = self.h = None
         self.thread = threading.Thread(target=self._run, daemon=True)
+        if enabled:
+            try:
+                import pynvml
+                pynvml.nvmlInit()
+                # NVML indexes physical devices; honour CUDA_VISIBLE_DEVICES when it lists indices
+                vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+                ids = [int(x) for x in vis.split(",") if x.strip().isdigit()]
+                phys = ids[index] if index < len(ids) else index
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+                self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+                self.nv = pynvml
+            except Exception:
+                self.nv = None
 
     def _sample(self):
+        nv = self.nv
         try:
-            out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                  "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
-            parts = [p.strip() for p in out.strip().split(",")]
-            if len(parts) >= 6:
-                self.rows.append(parts)
+            self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+            self.bits |= int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
         except Exception:
             pass
 
     def _run(self):
         while not self.stop.is_set():
             self._sample()
-            self.stop.wait(0.1)
+            self.stop.wait(0.01)
 
     def __enter__(self):
-        self.thread.start()
+        if self.enabled and self.nv is not None:
+            self.thread.start()
         return self
 
     def __exit__(self, *a):
         self.stop.set()
-        self.thread.join(timeout=10)
+        if self.thread.is_alive():
+            self.thread.join(timeout=10)
+
+    def _smi_once(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            out = subprocess.run(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i",
+                                  str(self.index)], capture_output=True, text=True, timeout=10).stdout
+            p = [x.strip() for x in out.strip().split(",")]
+            return {"sm_mhz": float(p[0]), "sm_max_mhz": float(p[1]),
+                    "reasons": [n for i, n in enumerate(self.NAMES) if p[2 + i].lower().startswith("active")],
+                    "samples": 1, "source": "nvidia-smi after the timed region (NVML unavailable)"}
+        except Exception:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
 
     def summary(self):
-        if not self.rows:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        sm = sorted(float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit())
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in self.rows)]
-        mx = [float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()]
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(self.rows)}
+        if not self.enabled:
+            return None
+        if self.nv is None or not self.sm:
+            return self._smi_once()
+        nv = self.nv
+        masks = [nv.nvmlClocksEventReasonHwSlowdown, nv.nvmlClocksEventReasonHwThermalSlowdown,
+                 nv.nvmlClocksEventReasonSwThermalSlowdown, nv.nvmlClocksEventReasonSwPowerCap]
+        sm = sorted(self.sm)
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": self.mx,
+                "reasons": [n for n, m in zip(self.NAMES, masks) if self.bits & m],
+                "samples": len(sm), "source": "NVML, 10 ms period, during the timed region"}
 
 
 def make_workload(args, device):
@@ -233,7 +265,9 @@ def time_steps(fn, steps, warmup, device, barrier=None):
     torch.cuda.synchronize(device)
     if barrier:
         barrier()
-    per = sorted(a.elapsed_time(b) for a, b in ev)
+    raw = [a.elapsed_time(b) for a, b in ev]
+    time_steps.last = [round(x, 3) for x in raw]
+    per = sorted(raw)
     return t0.elapsed_time(t1) / steps, per[len(per) // 2], per[0]
 
 
@@ -423,6 +457,7 @@ def run_multi(args):
 
     with ClockSampler(local) as clk:
         ms_avg, ms_med, ms_min = time_steps(lambda: part.forward(B), args.steps, args.warmup, device, barrier)
+    step_list = time_steps.last
     # the three phases of a step, each timed alone on the compute stream (untimed region of the bench):
     # what the overlap has to hide, and what it cannot
     blocks = part.fwd
@@ -457,6 +492,7 @@ def run_multi(args):
                        "local_nnz_frac": stats[0].item() / max(nnz, 1),
                        "exchange_bytes_received_per_rank_max": gathered,
                        "l2": "operands >> L2; no flush needed"},
+            "ms_steps_rank0": step_list,
             "phase_ms_alone": {"local_block_spmm": ph_local, "exchange": ph_exch, "remote_block_spmm": ph_remote,
                                "note": "median of 5, each phase run alone, max over ranks; the step overlaps the first two"},
             "gpu_launches": (3 if args.exchange == "pull" else 2) * args.steps, "ms_median": ms_med, "ms_min": ms_min,

@@ -35,7 +35,7 @@ template <typename V>
 __global__ void __launch_bounds__(kPullWarps * 32)
 pull_rows_kernel(PeerBases bases, const int32_t* __restrict__ part, const int32_t* __restrict__ row,
                  char* __restrict__ out, int64_t src_pitch, int64_t out_pitch, int64_t n_rows,
-                 int vecs_per_row) {
+                 int64_t first_row, int vecs_per_row) {
   const int lane = threadIdx.x & 31;
   const int64_t n_warps = (int64_t)gridDim.x * kPullWarps;
   for (int64_t w = (int64_t)blockIdx.x * kPullWarps + (threadIdx.x >> 5); w * kPullRowsPerWarp < n_rows;
@@ -45,7 +45,9 @@ pull_rows_kernel(PeerBases bases, const int32_t* __restrict__ part, const int32_
     V* dst[kPullRowsPerWarp];
 #pragma unroll
     for (int j = 0; j < kPullRowsPerWarp; ++j) {
-      const int64_t r = min(r0 + j, n_rows - 1);   // clamp: duplicates rewrite the same bytes
+      int64_t r = min(r0 + j, n_rows - 1);   // clamp: duplicates rewrite the same bytes
+      r += first_row;                        // rotated start (see gcnb_pull_rows)
+      if (r >= n_rows) r -= n_rows;
       src[j] = reinterpret_cast<const V*>(bases.p[__ldg(part + r)] + (int64_t)__ldg(row + r) * src_pitch);
       dst[j] = reinterpret_cast<V*>(out + r * out_pitch);
     }
@@ -122,8 +124,9 @@ int gcnb_peer_close(int device, void* ptr) {
 
 int gcnb_pull_rows(const void* const* bases, int n_parts, int64_t src_pitch_bytes,
                    const int32_t* part, const int32_t* row, void* out, int64_t out_pitch_bytes,
-                   int64_t n_rows, int64_t row_bytes, void* stream) {
+                   int64_t n_rows, int64_t row_bytes, int64_t first_row, void* stream) {
   GCNB_REQUIRE(n_rows >= 0 && row_bytes >= 0, "negative size");
+  GCNB_REQUIRE(first_row >= 0 && (first_row < n_rows || n_rows == 0), "first_row out of range");
   if (n_rows == 0 || row_bytes == 0) return GCNB_OK;
   GCNB_REQUIRE(bases && part && row && out, "null pointer");
   GCNB_REQUIRE(n_parts >= 1 && n_parts <= kMaxParts, "n_parts = %d (1..%d)", n_parts, kMaxParts);
@@ -147,13 +150,13 @@ int gcnb_pull_rows(const void* const* bases, int n_parts, int64_t src_pitch_byte
   cudaStream_t s = (cudaStream_t)stream;
   if (align % 16 == 0)
     pull_rows_kernel<uint4><<<(unsigned)blocks, kPullWarps * 32, 0, s>>>(
-        pb, part, row, (char*)out, src_pitch_bytes, out_pitch_bytes, n_rows, (int)(row_bytes / 16));
+        pb, part, row, (char*)out, src_pitch_bytes, out_pitch_bytes, n_rows, first_row, (int)(row_bytes / 16));
   else if (align % 4 == 0)
     pull_rows_kernel<uint32_t><<<(unsigned)blocks, kPullWarps * 32, 0, s>>>(
-        pb, part, row, (char*)out, src_pitch_bytes, out_pitch_bytes, n_rows, (int)(row_bytes / 4));
+        pb, part, row, (char*)out, src_pitch_bytes, out_pitch_bytes, n_rows, first_row, (int)(row_bytes / 4));
   else
     pull_rows_kernel<unsigned char><<<(unsigned)blocks, kPullWarps * 32, 0, s>>>(
-        pb, part, row, (char*)out, src_pitch_bytes, out_pitch_bytes, n_rows, (int)row_bytes);
+        pb, part, row, (char*)out, src_pitch_bytes, out_pitch_bytes, n_rows, first_row, (int)row_bytes);
   GCNB_CHECK_CUDA(cudaGetLastError());
   return GCNB_OK;
 }

@@ -201,6 +201,10 @@ class PartitionedSpMM:
             remote, halo_part, halo_row = compact_halo(remote, self.bounds, stride)
             blocks["remote_csr"] = remote
             blocks["halo_part_np"], blocks["halo_row_np"] = halo_part, halo_row
+            # every rank starts its pull at the rows of the NEXT rank and wraps around, so that the
+            # ranks read from different owners at any moment (see gcnb_pull_rows)
+            first = int(np.searchsorted(halo_part, self.rank + 1, side="left"))
+            blocks["halo_first"] = first if first < len(halo_part) else 0
             blocks["halo_part"] = torch.from_numpy(halo_part).to(self.device)
             blocks["halo_row"] = torch.from_numpy(halo_row).to(self.device)
             n_remote_cols = max(len(halo_row), 1)
@@ -279,7 +283,7 @@ class PartitionedSpMM:
             _ffi.call("gcnb_pull_rows", ex.bases(slot), self.world, k * 4,
                       ctypes.c_void_p(blocks["halo_part"].data_ptr()),
                       ctypes.c_void_p(blocks["halo_row"].data_ptr()), ctypes.c_void_p(halo.data_ptr()),
-                      k * 4, n_halo, k * 4,
+                      k * 4, n_halo, k * 4, blocks["halo_first"],
                       ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream))
         return halo
 

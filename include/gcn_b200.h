@@ -119,7 +119,10 @@ int gcnb_xw(const float* X, int64_t ldx, int trans_x, const float* W, int64_t ld
  * halo rows a rank needs straight out of the owners' HBM:
  *     out[i, :] = bases[part[i]][row[i], :]          (row_bytes bytes per row)
  * bases: HOST array of n_parts device pointers (own buffer or opened peers; entries never read may
- * be null); part,row: DEVICE int32[n_rows]; out: DEVICE.  Ordering between ranks (a block must be
+ * be null); part,row: DEVICE int32[n_rows]; out: DEVICE.  The rows are processed starting at index
+ * first_row and wrapping around: with the list sorted by owner, rank p passes the index of its first
+ * row owned by rank p+1, so that at any moment the ranks read from DIFFERENT owners instead of all
+ * draining GPU 0 first (8 GPUs, products-shaped: 1.75 -> see DESIGN.md §6).  Ordering between ranks (a block must be
  * written before a peer pulls it, and pulled before it is overwritten) is the caller's: see
  * gcn_b200/dist.py.
  * ------------------------------------------------------------------------------------------- */
@@ -130,7 +133,7 @@ int gcnb_peer_open(int device, const unsigned char* handle, void** ptr_out);
 int gcnb_peer_close(int device, void* ptr);
 int gcnb_pull_rows(const void* const* bases, int n_parts, int64_t src_pitch_bytes,
                    const int32_t* part, const int32_t* row, void* out, int64_t out_pitch_bytes,
-                   int64_t n_rows, int64_t row_bytes, void* stream);
+                   int64_t n_rows, int64_t row_bytes, int64_t first_row, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Host graph preprocessing (bit-exact with the reference).  All arrays HOST memory.

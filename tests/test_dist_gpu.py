@@ -33,13 +33,14 @@ def test_pull_rows_single_process():
         part_d, row_d = torch.from_numpy(part).to(dev), torch.from_numpy(row).to(dev)   # keep alive
         _ffi.call("gcnb_pull_rows", bases, 3, k * 4, ctypes.c_void_p(part_d.data_ptr()),
                   ctypes.c_void_p(row_d.data_ptr()), ctypes.c_void_p(out.data_ptr()),
-                  k * 4, n_out, k * 4, ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream))
+                  k * 4, n_out, k * 4, (k * 37) % n_out,
+                  ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream))
         torch.cuda.synchronize()
         want = np.stack([bufs[p][r].cpu().numpy() for p, r in zip(part, row)])
         assert np.array_equal(out.cpu().numpy(), want)     # a copy: bit-exact
     # argument errors are reported, not crashed on
-    assert _ffi.lib.gcnb_pull_rows(None, 3, 4, None, None, None, 4, 5, 4, None) == -1
-    assert _ffi.lib.gcnb_pull_rows(bases, 99, 4, None, None, None, 4, 0, 4, None) == 0   # empty: no-op
+    assert _ffi.lib.gcnb_pull_rows(None, 3, 4, None, None, None, 4, 5, 4, 0, None) == -1
+    assert _ffi.lib.gcnb_pull_rows(bases, 99, 4, None, None, None, 4, 0, 4, 0, None) == 0   # empty: no-op
 
 
 def _free_port():

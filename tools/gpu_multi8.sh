@@ -13,9 +13,9 @@ except Exception as e: print("  ERR", e)
 PY
   tail -2 $o/${tag}_$name.err | cut -c1-300
 }
-runm 8 spmm_n8_pull --exchange pull
-runm 8 spmm_n8_allgather --exchange allgather
+timeout 300 python -m pytest tests/test_dist_gpu.py -x -q 2>&1 | tail -2
+for c in 1 2 4; do GCNB_PULL_CTAS=$c runm 8 spmm_n8_pull_ctas$c --exchange pull; done
 runm 4 spmm_n4_pull --exchange pull
+runm 2 spmm_n2_pull --exchange pull
 runm 8 epoch_n8_pull --exchange pull --mode epoch
-runm 4 epoch_n4_pull --exchange pull --mode epoch
 runm 8 rmat_s24_n8_pull --exchange pull --workload rmat --scale 24 --edge-factor 16 --k 128
