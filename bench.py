@@ -60,18 +60,19 @@ def parse():
     ap.add_argument("--exchange", default="pull", choices=["pull", "allgather"],
                     help="N>1: how remote feature rows arrive — our P2P halo pull over NVLink peer memory, "
                          "or an NCCL all-gather of the whole operand")
+    ap.add_argument("--assoc", default="auto", choices=["auto", "reference"],
+                    help="epoch mode: 'reference' = gc1 Â·(X·W1), gc2 (Â·H)·W2 as pygcn/gcn5.py builds them; 'auto' = "
+                         "the same layers evaluated at the narrower SpMM width with Â·X cached (gcn_b200/model.py)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
 
 
 def kernel_launches_per_spmm(info, k, dtype):
-    """Kernels one gcnb_spmm call launches (spmm.cu: launch_vec / launch_one), counted from the plan."""
-    vec = 4 if dtype == "f32" else (8 if (k % 8 == 0 and k <= 64) else 4)
-    while k % vec:
-        vec //= 2
-    nvec = (k + vec - 1) // vec
-    if nvec > 16:   # whole warp per row -> stream class
+    """Kernels one gcnb_spmm call launches (spmm.cu: launch_vec), counted from the plan: every width
+    runs a stream-class kernel (packed for narrow rows) + one fixed-order reduction if a row was cut."""
+    packed = int(os.environ.get("GCNB_PACKED", "8")) >= 2 and info["nnz"] >= 24 * info["m"]
+    if packed or k > 64:
         return 1 + (info["stream_rows_split"] > 0)
     return 1 + (info["block_items"] > 0) + (info["rows_split"] > 0)
 
@@ -362,6 +363,7 @@ def epoch_line(args, name, n, nnz, world, ms_avg, ms_med, ms_min, clocks, extra)
            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
            "config": {"workload": f"{name} 2-layer GCN {nfeat}->{nhid}->{nclass} training epoch "
                                   "(forward, NLL on 5 % of the vertices, backward, Adam); pygcn/gcn5.py:146-262",
+                      "association": args.assoc,
                       "n": n, "nnz": nnz, "l2": "operands >> L2; no flush needed"},
            "ms_median": ms_med, "ms_min": ms_min, "clocks": clocks, "e2e": None}
     out.update(extra)
@@ -382,14 +384,15 @@ def run_epoch_single(args):
     labels = torch.randint(0, nclass, (n,), device=device, generator=g)
     idx_train = torch.arange(n // 20, device=device)
     torch.manual_seed(15)
-    net = gmodel.GCN(nfeat, nhid, nclass, dataset=args.workload, device=device)
+    net = gmodel.GCN(nfeat, nhid, nclass, dataset=args.workload, device=device, association=args.assoc)
     net.features, net.adj_norm, net.labels = X, plan, labels
     opt = torch.optim.Adam(net.parameters(), lr=net.lr, weight_decay=net.weight_decay)
     with ClockSampler(0) as clk:
         ms_avg, ms_med, ms_min = time_steps(lambda: net._step(opt, labels, idx_train), args.steps, args.warmup, device)
     print(json.dumps(epoch_line(args, name, n, nnz, 1, ms_avg, ms_med, ms_min, clk.summary(),
-                                {"gpu_launches": None, "note": "4 SpMMs + 6 tcgen05 GEMMs of ours per epoch; "
-                                 "dropout / log_softmax / NLL / Adam are torch elementwise kernels"})))
+                                {"gpu_launches": None, "note": ("2 SpMMs (width nclass) + 6 tcgen05 GEMMs of ours per epoch, Â·X cached; "
+                                                                if args.assoc == "auto" else "4 SpMMs + 6 tcgen05 GEMMs of ours per epoch; ")
+                                 + "dropout / log_softmax / NLL / Adam are torch elementwise kernels"})))
 
 
 def run_epoch_multi(args):
@@ -410,7 +413,7 @@ def run_epoch_multi(args):
     labels = torch.randint(0, nclass, (part.m_local,), device=device, generator=g)
     n_train = n // 20
     idx_train = torch.arange(max(0, min(part.hi, n_train) - part.lo), device=device)
-    net = gdist.PartitionedGCN(part, nfeat, nhid, nclass)
+    net = gdist.PartitionedGCN(part, nfeat, nhid, nclass, association=args.assoc)
 
     def barrier():
         dist.barrier(device_ids=[local])

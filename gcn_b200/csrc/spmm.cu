@@ -335,12 +335,49 @@ static int launch_one(const LaunchArgs& a) {
   return GCNB_OK;
 }
 
+// narrow feature rows: S non-zeros per warp-wide gather (spmm_stream_packed_kernel), one launch for
+// every row class (+ the split-row reduction)
+template <typename TB, int VEC, int S>
+static int launch_packed(const LaunchArgs& a) {
+  const Matrix& M = *a.M;
+  if (M.n_segs == 0) return GCNB_OK;
+  constexpr int U = 4;
+  constexpr int MINB = (sizeof(TB) == 2 && VEC <= 4) ? 10 : 8;
+  const int64_t gs = (M.n_segs + kStreamWarps - 1) / kStreamWarps;
+  if (gs > 0x7fffffffLL || a.ldb * (int64_t)sizeof(TB) > 0xffffffffLL)
+    return set_error(GCNB_ERR_UNSUPPORTED, "matrix too large for one grid");
+  spmm_stream_packed_kernel<TB, VEC, S, U, MINB><<<(unsigned)gs, kStreamWarps * 32, 0, a.stream>>>(
+      M.segs, (int)M.n_segs, M.rowptr, M.cv, (const TB*)a.B, (uint32_t)(a.ldb * sizeof(TB)), a.C, a.ldc,
+      a.partials, a.k, a.bias, a.epi);
+  GCNB_CHECK_CUDA(cudaGetLastError());
+  if (M.s_n_split > 0) {
+    spmm_reduce_kernel<<<(unsigned)M.s_n_split, 128, 0, a.stream>>>(
+        M.s_split_rows, M.s_split_ptr, a.partials, a.C, a.ldc, a.k, a.bias, a.epi);
+    GCNB_CHECK_CUDA(cudaGetLastError());
+  }
+  return GCNB_OK;
+}
+
 template <typename TB, int VEC, int NVMAX>
 static int launch_vec(const LaunchArgs& a) {
   const int nvec = (a.k + VEC - 1) / VEC;  // vectors per feature row
-  if (nvec <= 4) return launch_one<TB, VEC, 4, 1>(a);
-  if (nvec <= 8) return launch_one<TB, VEC, 8, 1>(a);
-  if (nvec <= 16) return launch_one<TB, VEC, 16, 1>(a);
+  // GCNB_PACKED = largest S the packed stream kernel may use (0: lane-group / block kernels instead)
+  static const int packed = getenv("GCNB_PACKED") ? atoi(getenv("GCNB_PACKED")) : 8;
+  // Measured (profiles/r01_v_*): products-shaped (50 nnz/row) k=32: 1.86 ms packed vs 2.87 ms lane-group
+  // kernel, k=48: 2.58 vs 3.73; Reddit-shaped k=48: 1.05 vs 1.53; but arxiv-shaped (15 nnz/row) k=40:
+  // 0.097 vs 0.080 — with short rows the fold at every row end outweighs the saved requests, and the
+  // lane-group kernel (several rows side by side in a warp) wins.
+  if (packed >= 2 && nvec <= 16 && a.M->nnz >= 24 * a.M->m) {
+    if (nvec <= 4 && packed >= 8) return launch_packed<TB, VEC, 8>(a);
+    if (nvec <= 8 && packed >= 4) return launch_packed<TB, VEC, 4>(a);
+    return launch_packed<TB, VEC, 2>(a);
+  }
+  // rows needing more than `stream_min` lanes go to the whole-warp stream class, narrower ones to the
+  // lane-group kernel (several rows per warp)
+  static const int stream_min = getenv("GCNB_STREAM_MIN_NVEC") ? atoi(getenv("GCNB_STREAM_MIN_NVEC")) : 16;
+  if (nvec <= 4 && stream_min >= 4) return launch_one<TB, VEC, 4, 1>(a);
+  if (nvec <= 8 && stream_min >= 8) return launch_one<TB, VEC, 8, 1>(a);
+  if (nvec <= 16 && stream_min >= 16) return launch_one<TB, VEC, 16, 1>(a);
   if (nvec <= 32) return launch_one<TB, VEC, 32, 1>(a);
   // wide rows: whole warp per row, NV vectors per lane, as few column tiles as possible
   const int tiles = (nvec + 32 * NVMAX - 1) / (32 * NVMAX);
@@ -368,8 +405,9 @@ static int spmm_dispatch(const Matrix& M, const void* B, int b_dtype, int64_t ld
   int rc;
   // vector width: limited by k, both leading dimensions and base alignment (C is stored with
   // min(VEC,4) floats per store)
+  static const int max_vec = getenv("GCNB_MAX_VEC") ? atoi(getenv("GCNB_MAX_VEC")) : 4;   // experiments
   if (b_dtype == GCNB_F32) {
-    if (k % 4 == 0 && ldb % 4 == 0 && ldc % 4 == 0 && aligned(B, 16) && aligned(C, 16))
+    if (max_vec >= 4 && k % 4 == 0 && ldb % 4 == 0 && ldc % 4 == 0 && aligned(B, 16) && aligned(C, 16))
       rc = launch_vec<float, 4, 4>(a);
     else if (k % 2 == 0 && ldb % 2 == 0 && ldc % 2 == 0 && aligned(B, 8) && aligned(C, 8))
       rc = launch_vec<float, 2, 4>(a);
@@ -380,7 +418,8 @@ static int spmm_dispatch(const Matrix& M, const void* B, int b_dtype, int64_t ld
     // loads over half as many lanes (products-shaped, k = 128: 3.1 vs 4.9 ms, profiles/r01_j_*), so
     // 16-byte loads are kept for the narrow lane-group kernel only
     const bool v4ok = k % 4 == 0 && ldb % 4 == 0 && ldc % 4 == 0 && aligned(B, 8) && aligned(C, 16);
-    if (v4ok && k > 64)
+    static const int bf16_v8_max = getenv("GCNB_BF16_V8_MAX") ? atoi(getenv("GCNB_BF16_V8_MAX")) : 64;
+    if (v4ok && k > bf16_v8_max)
       rc = launch_vec<__nv_bfloat16, 4, 4>(a);
     else if (k % 8 == 0 && ldb % 8 == 0 && ldc % 4 == 0 && aligned(B, 16) && aligned(C, 16))
       rc = launch_vec<__nv_bfloat16, 8, 2>(a);

@@ -705,6 +705,163 @@ spmm_stream_kernel(const Seg* __restrict__ segs, int n_segs, const int32_t* __re
   while (row < r1) flush();   // the last row of the segment and any trailing empty rows
 }
 
+// ---- stream class, narrow feature rows: S non-zeros per warp-wide load ---------------------------
+// Measured (profiles/r01_t_*, r01_u_*): on the products-shaped graph the stream kernel above costs
+// ~2.5 ms for ANY width between 24 and 64 floats and 3.6 ms for 100..128 — it is bound by the number of
+// warp-wide gather requests (one per non-zero, ~6 cycles per request per SM), not by bytes.  When a
+// feature row needs only L = 32/S lanes, this variant lets ONE load instruction fetch the rows of S
+// consecutive non-zeros of the stream (sub-group s of L lanes takes non-zero base+s), which divides the
+// request count by S.  Each sub-group keeps its own partial sums; at a row end they are folded with a
+// fixed xor butterfly (deterministic) and sub-group 0 writes the row.  Everything else — segments,
+// slab, ring, partial-row pieces — is as in spmm_stream_kernel.
+template <typename TB, int VEC, int S, int U, int MINB>
+__global__ void __launch_bounds__(kStreamWarps * 32, MINB)
+spmm_stream_packed_kernel(const Seg* __restrict__ segs, int n_segs, const int32_t* __restrict__ rowptr,
+                          const int2* __restrict__ cv, const TB* __restrict__ B, uint32_t ldb_bytes,
+                          float* __restrict__ C, int64_t ldc, float* __restrict__ partials, int k,
+                          const float* __restrict__ bias, int epi_arg) {
+  constexpr int L = 32 / S;     // lanes per sub-group
+  constexpr int BLK = U * S;    // non-zeros per ring turn
+  static_assert(S >= 2 && 32 % BLK == 0, "a ring turn must not straddle a slab");
+  __shared__ alignas(16) int2 s_cv[kStreamWarps][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int s = blockIdx.x * kStreamWarps + warp;
+  if (s >= n_segs) return;
+  const int4 sg = __ldg(reinterpret_cast<const int4*>(segs) + s);
+  const int sub = lane / L, li = lane % L;
+  int row = sg.x;
+  const bool piece = sg.y < 0;
+  const int r1 = piece ? row + 1 : sg.y;
+  const int r1s = sg.y;
+  const int coff = li * VEC;
+  const bool cok = coff < k;
+  const char* bl = reinterpret_cast<const char*>(B + (cok ? coff : 0));
+
+  int rbase = row;
+  const int z0 = sg.z;
+  const int total = sg.w - z0;
+  int rp_c = piece ? sg.w : __ldg(rowptr + min(rbase + 1 + lane, r1));
+  int rend = __shfl_sync(0xffffffffu, rp_c, 0) - z0;
+
+  float acc[VEC];
+#pragma unroll
+  for (int x = 0; x < VEC; ++x) acc[x] = 0.f;
+
+  auto flush = [&]() {
+#pragma unroll
+    for (int o = L; o < 32; o <<= 1)
+#pragma unroll
+      for (int x = 0; x < VEC; ++x) acc[x] += __shfl_xor_sync(0xffffffffu, acc[x], o);
+    if (sub == 0 && cok) {
+      float* crow = r1s < 0 ? partials + (int64_t)(-1 - r1s) * k : C + (int64_t)row * ldc;
+      const int epi = r1s < 0 ? 0 : epi_arg;
+      float o[VEC];
+      if (epi & GCNB_EPI_ACCUM) {
+#pragma unroll
+        for (int x = 0; x < VEC; ++x) acc[x] += crow[coff + x];
+      }
+#pragma unroll
+      for (int x = 0; x < VEC; ++x) o[x] = epilogue(acc[x], bias, coff + x, epi);
+      store_vec<VEC>(crow + coff, o);
+    }
+#pragma unroll
+    for (int x = 0; x < VEC; ++x) acc[x] = 0.f;
+    ++row;
+    int idx = row - rbase;
+    if (idx == 32) {
+      rbase = row;
+      rp_c = __ldg(rowptr + min(rbase + 1 + lane, r1));
+      idx = 0;
+    }
+    rend = __shfl_sync(0xffffffffu, rp_c, idx) - z0;
+  };
+
+  float av[U];
+  RawVec<TB, VEC> bv[U];
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    av[u] = 0.f;
+    bv[u].zero();
+  }
+  auto consume = [&](int u) {
+    float b[VEC];
+    bv[u].get(b);
+    if constexpr (VEC % 2 == 0) {
+#pragma unroll
+      for (int x = 0; x < VEC; x += 2) ffma2(acc[x], acc[x + 1], av[u], b[x], b[x + 1]);
+    } else {
+#pragma unroll
+      for (int x = 0; x < VEC; ++x) acc[x] = fmaf(av[u], b[x], acc[x]);
+    }
+  };
+
+  uint32_t slab_a, slab_l;
+  asm volatile("mov.u32 %0, %1;" : "=r"(slab_a) : "r"((uint32_t)__cvta_generic_to_shared(s_cv[warp])));
+  asm volatile("mov.u32 %0, %1;" : "=r"(slab_l) : "r"(slab_a + 8u * (uint32_t)lane));
+  const uint32_t slab_s = slab_a + 8u * (uint32_t)sub;   // this sub-group's entry inside a slot
+  const int2* src = cv + z0;
+  int2 e = make_int2(0, 0);
+  if (lane < total) e = ld_stream_int2(src + lane);
+  auto refill = [&](int at) {
+    __syncwarp();
+    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(slab_l), "r"(e.x), "r"(e.y) : "memory");
+    __syncwarp();
+    if (at + 32 + lane < total) e = ld_stream_int2(src + at + 32 + lane);
+  };
+  // slot u <- non-zeros at .. at+S-1 (at is a multiple of S), one per sub-group
+  auto issue_full = [&](int u, int at) {
+    int2 q;
+    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(q.x), "=r"(q.y) : "r"(slab_s + 8u * (uint32_t)(at & 31)) : "memory");
+    av[u] = __int_as_float(q.y);
+    if (cok) bv[u].load(reinterpret_cast<const TB*>(bl + (uint64_t)(uint32_t)q.x * ldb_bytes));
+  };
+  auto issue_tail = [&](int u, int at) {
+    int2 q;
+    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(q.x), "=r"(q.y) : "r"(slab_s + 8u * (uint32_t)(at & 31)) : "memory");
+    const bool valid = at + sub < total;   // entries past the end of the stream are stale
+    av[u] = valid ? __int_as_float(q.y) : 0.f;
+    if (valid && cok) bv[u].load(reinterpret_cast<const TB*>(bl + (uint64_t)(uint32_t)q.x * ldb_bytes));
+    else bv[u].zero();
+  };
+
+  refill(0);
+#pragma unroll
+  for (int u = 0; u < U; ++u)
+    if (u * S < total) issue_tail(u, u * S);
+
+  for (int g = 0; g < total; g += BLK) {
+    const int nxt = g + BLK;
+    if ((nxt & 31) == 0 && nxt < total) refill(nxt);
+    if (nxt <= rend && nxt + BLK <= total) {
+      // fast path: no row end inside this turn, the next turn is complete
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        consume(u);
+        issue_full(u, nxt + u * S);
+      }
+    } else {
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int base = g + u * S;          // slot u holds stream positions [base, base+S)
+        if (base < total) {
+          const int pos = base + sub;
+          const int stop = min(base + S, total);
+          int done = base;
+          while (true) {
+            while (done == rend) flush();      // the current row ends here (also skips empty rows)
+            const int lim = min(rend, stop);
+            if (pos >= done && pos < lim) consume(u);
+            done = lim;
+            if (done >= stop) break;
+          }
+        }
+        if (nxt + u * S < total) issue_tail(u, nxt + u * S);
+      }
+    }
+  }
+  while (row < r1) flush();
+}
+
 // ---- block class -------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return (uint32_t)__cvta_generic_to_shared(p);

@@ -380,10 +380,12 @@ class PartitionedGCN(torch.nn.Module):
     (SURVEY.md §8e).  One epoch = 4 gathered SpMMs (2 forward, 2 backward) + 6 dense products."""
 
     def __init__(self, part: PartitionedSpMM, nfeat, nhid, nclass, dropout=0.5, lr=0.01,
-                 weight_decay=5e-4, seed=15):
+                 weight_decay=5e-4, seed=15, association="reference"):
         super().__init__()
         from .layers import GraphConvolution, GraphConvolution2
         self.part = part
+        self.association = association   # see gcn_b200.model: 'auto' = SpMM at the narrower width
+        self._ax = None
         g = torch.Generator().manual_seed(seed)   # identical replicas on every rank
         self.gc1 = GraphConvolution(nfeat, nhid)
         self.gc2 = GraphConvolution2(nhid, nclass)
@@ -396,13 +398,27 @@ class PartitionedGCN(torch.nn.Module):
 
     def forward(self, x_local):
         from . import gemm
-        nhid = self.gc1.weight.shape[1]
-        support = gemm.xw(x_local, self.gc1.weight, out=self.part.next_operand(nhid))   # straight into the exchange slot
-        h = torch.relu(spmm(self.part, support) + self.gc1.bias)
-        h = torch.nn.functional.dropout(h, self.dropout, training=self.training)
-        s2 = spmm(self.part, h)
-        out = gemm.xw(s2, self.gc2.weight, bias=self.gc2.bias)
-        return torch.nn.functional.log_softmax(out, dim=1)
+        F = torch.nn.functional
+        nfeat, nhid = self.gc1.weight.shape
+        nclass = self.gc2.weight.shape[1]
+        if self.association == "auto" and nfeat <= nhid:
+            if self._ax is None or self._ax[0] != x_local.data_ptr():
+                with torch.no_grad():   # Â·X once: X is constant over the epochs
+                    self._ax = (x_local.data_ptr(), self.part.forward(x_local))
+            h = gemm.xw(self._ax[1], self.gc1.weight, bias=self.gc1.bias, relu=True)
+        else:
+            support = gemm.xw(x_local, self.gc1.weight, out=self.part.next_operand(nhid))   # straight into the exchange slot
+            h = torch.relu(spmm(self.part, support) + self.gc1.bias)
+        h = F.dropout(h, self.dropout, training=self.training)
+        if self.association == "auto" and nclass < nhid:
+            pad = (-nclass) % 4
+            w = F.pad(self.gc2.weight, (0, pad)) if pad else self.gc2.weight
+            s2 = gemm.xw(h, w, out=self.part.next_operand(nclass + pad))
+            out = spmm(self.part, s2)[:, :nclass] + self.gc2.bias
+        else:
+            s2 = spmm(self.part, h)
+            out = gemm.xw(s2, self.gc2.weight, bias=self.gc2.bias)
+        return F.log_softmax(out, dim=1)
 
     def step(self, x_local, labels_local, idx_train_local, n_train_global):
         """One training epoch (forward, NLL on the local training rows, backward, gradient

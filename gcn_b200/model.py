@@ -13,6 +13,14 @@ layer-2 choice (A·(XW) for pubmed/flickr, (A·X)·W otherwise, gcn5.py:160-163)
   * backward uses Âᵀ; ``_train_with_val`` / ``predict`` work with the same forward signature
     (they are broken in gcn6, SURVEY.md §4 defect 4).
   * ReLU of layer 1 is fused into the producing kernel's epilogue.
+  * ``association='auto'`` (constructor; default ``'reference'``) evaluates the same two layers
+    ``Â·X·W + b`` in the cheaper of the two orders the reference itself offers as GraphConvolution
+    (Â·(X·W)) and GraphConvolution2 ((Â·X)·W) — cf. gcn6.py:215-218 — so that the SpMM always runs at
+    the narrower width: layer 1 with nfeat <= nhid becomes (Â·X)·W1 with Â·X computed ONCE per fit
+    (X is constant, so neither the forward nor the backward of layer 1 contains an SpMM any more),
+    layer 2 with nclass < nhid becomes Â·(H·W2) (SpMM at width nclass, padded to a multiple of 4,
+    instead of nhid).  Same mathematics, different rounding order: outputs agree with the
+    reference association to ~1e-6 relative (tests/test_layers_gpu.py).
 """
 from __future__ import annotations
 
@@ -24,8 +32,8 @@ import torch.nn as nn
 import torch.nn.functional as F
 import torch.optim as optim
 
-from . import graph, ops
-from .layers import GraphConvolution, GraphConvolution2
+from . import gemm, graph, ops
+from .layers import GraphConvolution, GraphConvolution2, _is_sparse
 
 
 def accuracy(output, labels):
@@ -36,9 +44,14 @@ def accuracy(output, labels):
 
 class GCN(nn.Module):
     def __init__(self, nfeat, nhid, nclass, dataset="dataset", dropout=0.5, lr=0.01,
-                 weight_decay=5e-4, with_relu=True, with_bias=True, device=None):
+                 weight_decay=5e-4, with_relu=True, with_bias=True, device=None,
+                 association="reference"):
         super().__init__()
         assert device is not None, "Please specify 'device'!"
+        if association not in ("reference", "auto"):
+            raise ValueError("association must be 'reference' or 'auto'")
+        self.association = association
+        self._ax_cache = None   # (features data_ptr, id(adj), Â·X)
         self.device = torch.device(device)
         self.nfeat = nfeat
         self.hidden_sizes = [nhid]
@@ -66,10 +79,47 @@ class GCN(nn.Module):
 
     def forward(self, x, adj, name="dataset"):
         """adj: normalised adjacency (torch sparse tensor on the GPU or an SpmmPlan)."""
+        if self.association == "auto":
+            return self._forward_min_width(x, adj)
         x = self.gc1(x, adj, relu=self.with_relu)
         x = F.dropout(x, self.dropout, training=self.training)
         x = self.gc2(x, adj)
         return F.log_softmax(x, dim=1)
+
+    def invalidate_cache(self):
+        """Forget the cached Â·X (call after changing the features in place)."""
+        self._ax_cache = None
+
+    def _aggregated_features(self, x, adj):
+        key = (x.data_ptr(), id(adj))
+        if self._ax_cache is None or self._ax_cache[:2] != key:
+            with torch.no_grad():
+                self._ax_cache = key + (ops.plan_for(adj).spmm(x),)
+        return self._ax_cache[2]
+
+    def _forward_min_width(self, x, adj):
+        nfeat, nhid = self.gc1.weight.shape
+        if not _is_sparse(x) and not x.requires_grad and nfeat <= nhid:
+            # (Â·X)·W1 + b1 with Â·X cached: no SpMM in layer 1, forward or backward
+            h = gemm.xw(self._aggregated_features(x, adj), self.gc1.weight, bias=self.gc1.bias,
+                        relu=self.with_relu)
+        else:
+            h = self.gc1(x, adj, relu=self.with_relu) if isinstance(self.gc1, GraphConvolution) else self.gc1(x, adj)
+        h = F.dropout(h, self.dropout, training=self.training)
+        nh, nc = self.gc2.weight.shape
+        if nc < nh:
+            # Â·(H·W2) + b2: SpMM at width nclass (zero-padded to 4 floats for 128-bit rows)
+            pad = (-nc) % 4
+            w = F.pad(self.gc2.weight, (0, pad)) if pad else self.gc2.weight
+            b = self.gc2.bias
+            if b is not None and pad:
+                b = F.pad(b, (0, pad))
+            out = ops.spmm(adj, gemm.xw(h, w), bias=b)
+            if pad:
+                out = out[:, :nc]
+        else:
+            out = self.gc2(h, adj)
+        return F.log_softmax(out, dim=1)
 
     def initialize(self):
         self.gc1.reset_parameters()
@@ -144,6 +194,7 @@ class GCN(nn.Module):
             raise RuntimeError("gcn_b200: GCN must live on a CUDA device (no CPU fallback)")
         if initialize:
             self.initialize()
+        self._ax_cache = None
         self.features, self.adj_norm, self.labels, self.vomp = self._prepare(
             features, adj, labels, normalize, reorder)
         idx_train = self._map_index(idx_train)

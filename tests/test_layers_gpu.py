@@ -89,3 +89,32 @@ def test_fit_trains_and_reorder_is_consistent(golden_gcn, reorder):
     # with validation + early stopping paths (broken in the reference's gcn6, SURVEY.md §4 defect 4)
     m.fit(torch.from_numpy(x), a, labels, idx_train, idx_val=idx_test, train_iters=10, reorder=reorder)
     m.fit(torch.from_numpy(x), a, labels, idx_train, idx_val=idx_test, train_iters=10, patience=3, reorder=reorder)
+
+
+@pytest.mark.parametrize("dataset", ["cora", "pubmed"])
+def test_min_width_association_matches_reference_association(golden_gcn, dataset):
+    """association='auto' ((Â·X)·W1 with Â·X cached, Â·(H·W2)) is the same function as the reference
+    association: outputs, loss and every gradient agree to fp32 rounding."""
+    g = golden_gcn
+    n, a, _ = _load(g)
+    rng = np.random.default_rng(4)
+    X = torch.from_numpy(rng.standard_normal((n, 12)).astype(np.float32))
+    labels = rng.integers(0, 7, n)
+    idx = torch.arange(0, n, 2, device=DEV)
+    res = {}
+    for assoc in ("reference", "auto"):
+        torch.manual_seed(3)
+        m = model.GCN(nfeat=12, nhid=16, nclass=7, dataset=dataset, dropout=0.0, device=DEV, association=assoc)
+        x, plan, y, _ = m._prepare(X, a, labels, True, None)
+        m.train()
+        for _ in range(2):      # second pass goes through the cached Â·X
+            m.zero_grad()
+            out = m.forward(x, plan)
+            loss = F.nll_loss(out[idx], y[idx])
+            loss.backward()
+        res[assoc] = (out.detach().cpu().numpy(), loss.item(),
+                      [p.grad.cpu().numpy() for p in (m.gc1.weight, m.gc1.bias, m.gc2.weight, m.gc2.bias)])
+    assert rel_err(res["auto"][0], res["reference"][0]) < TOL
+    assert abs(res["auto"][1] - res["reference"][1]) < 1e-5
+    for ga, gr in zip(res["auto"][2], res["reference"][2]):
+        assert ga.shape == gr.shape and rel_err(ga, gr) < 5e-5
