@@ -10,12 +10,14 @@ precision 2 bf16 operands.
 from __future__ import annotations
 
 import ctypes
+import os
 
 import torch
 
 from . import _ffi
 
 PRECISION_3XTF32, PRECISION_TF32, PRECISION_BF16 = 0, 1, 2
+_SWAP_DW = os.environ.get("GCNB_XW_SWAP_DW", "1") != "0"
 
 
 def _row_major(t: torch.Tensor) -> torch.Tensor:
@@ -83,7 +85,12 @@ class _XW(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             gX = gemm_raw(g, W.detach(), trans_b=True, precision=ctx.precision)      # dS · Wᵀ
         if ctx.needs_input_grad[1]:
-            gW = gemm_raw(X.detach(), g, trans_a=True, precision=ctx.precision)      # Xᵀ · dS
+            # Xᵀ·dS.  gcnb_xw lays its second operand out once per call (prep kernel, cost ∝ its size), so
+            # the narrower of X [M×K] and dS [M×N] goes second: dW = Xᵀ·dS or (dSᵀ·X)ᵀ
+            if X.shape[1] < g.shape[1] and _SWAP_DW:
+                gW = gemm_raw(g, X.detach(), trans_a=True, precision=ctx.precision).t().contiguous()
+            else:
+                gW = gemm_raw(X.detach(), g, trans_a=True, precision=ctx.precision)
         if ctx.has_bias and ctx.needs_input_grad[2]:
             gb = g.sum(dim=0)
         return gX, gW, gb, None, None, None

@@ -280,3 +280,42 @@ def test_full_size_properties(shape, k):
     # symmetric: <Y, AX> = <AY, X>
     a, b = (Y.double() * AX.double()).sum().item(), (AY.double() * X.double()).sum().item()
     assert abs(a - b) <= 1e-6 * max(abs(a), 1.0) + 1e-3
+
+
+def _dense_skew_graph(n=1800, e=90000, seed=21):
+    """Mean row length >= 24 (the packed stream kernel's dispatch condition, spmm.cu launch_vec) with
+    a heavy head: some rows beyond kSegLong = 1024 non-zeros are cut into pieces, plus empty-ish tails."""
+    A = random_normalized_graph(n, e, seed, "skew")
+    assert A.nnz >= 24 * A.shape[0] and np.diff(A.indptr).max() > 1024
+    return A
+
+
+@pytest.mark.parametrize("k", [1, 2, 4, 8, 12, 16, 20, 32, 36, 47, 48, 64])
+def test_packed_stream_kernel_narrow_widths(k):
+    """Narrow feature rows on a graph dense enough for the packed stream kernel (S = 2/4/8 non-zeros
+    per warp-wide gather): fp32 and bf16 operands, bias/ReLU epilogue, accumulate, bit-reproducible."""
+    A = _dense_skew_graph()
+    n = A.shape[0]
+    rng = np.random.default_rng(100 + k)
+    B = rng.standard_normal((n, k)).astype(np.float32)
+    bias = rng.standard_normal(k).astype(np.float32)
+    ref = SO.spmm_f64(A.indptr, A.indices, A.data, n, B)
+    plan = ops.SpmmPlan.from_scipy(A, device=DEV)
+    Bd = torch.from_numpy(B).to(DEV)
+    C = plan.spmm(Bd)
+    assert rel_err(C.cpu().numpy(), ref) < FP32_TOL
+    assert torch.equal(C, plan.spmm(Bd))
+    Ce = plan.spmm(Bd, bias=torch.from_numpy(bias).to(DEV), relu=True).cpu().numpy()
+    assert rel_err(Ce, np.maximum(ref + bias, 0)) < FP32_TOL
+    C0 = torch.from_numpy(rng.standard_normal((n, k)).astype(np.float32)).to(DEV)
+    want = C0.cpu().numpy().astype(np.float64) + ref
+    assert rel_err(plan.spmm(Bd, out=C0, accumulate=True).cpu().numpy(), want) < FP32_TOL
+    Bb = Bd.to(torch.bfloat16)
+    ref_b = SO.spmm_f64(A.indptr, A.indices, A.data, n, Bb.float().cpu().numpy())
+    assert rel_err(plan.spmm(Bb).cpu().numpy(), ref_b) < FP32_TOL     # same bf16 inputs: fp32 accumulation
+    assert rel_err(plan.spmm(Bb).cpu().numpy(), ref) < BF16_TOL
+    # padded rows (row pitch > k) in and out
+    Bp = torch.zeros(n, k + 4, device=DEV)[:, :k]
+    Bp.copy_(Bd)
+    Cp = torch.empty(n, k + 8, device=DEV)[:, :k]
+    assert rel_err(plan.spmm(Bp, out=Cp).cpu().numpy(), ref) < FP32_TOL
