@@ -55,7 +55,7 @@ def parse():
                     help="row pitch of B and C in elements (>= k; default k = contiguous rows)")
     ap.add_argument("--mode", default="spmm", choices=["spmm", "epoch"],
                     help="spmm: one C = A·B pass (headline); epoch: one 2-layer GCN training epoch")
-    ap.add_argument("--order", default="none", choices=["none", "deg", "rcm", "gorder"],
+    ap.add_argument("--order", default="none", choices=["none", "deg", "rcm", "gorder", "rabbit"],
                     help="host vertex reordering applied to the graph before the plan is built")
     ap.add_argument("--exchange", default="pull", choices=["pull", "allgather"],
                     help="N>1: how remote feature rows arrive — our P2P halo pull over NVLink peer memory, "
@@ -179,7 +179,8 @@ def make_workload(args, device):
         # host preprocessing of the path (renumber.cu / order_*.cu equivalents, bit-exact): timed,
         # reported, outside the SpMM step
         from gcn_b200 import graph
-        fn = {"deg": graph.renumber_deg, "rcm": graph.renumber_rcm, "gorder": graph.renumber_gorder}[args.order]
+        fn = {"deg": graph.renumber_deg, "rcm": graph.renumber_rcm, "gorder": graph.renumber_gorder,
+              "rabbit": graph.renumber_rabbit}[args.order]
         t0 = time.perf_counter()
         rp, ci, va, _vomp = fn(rp, ci, va)
         args.reorder_s = round(time.perf_counter() - t0, 2)

@@ -66,6 +66,7 @@ SIGNATURES = {
     "gcnb_perm_apply": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64]),
     "gcnb_renumber_gorder": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int]),
     "gcnb_renumber_dfs": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64]),
+    "gcnb_renumber_rabbit": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64]),
     "gcnb_renumber_rcm": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64]),
     "gcnb_renumber_deg": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int]),
     "gcnb_tile_count": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, _i64p]),
@@ -78,6 +79,7 @@ SIGNATURES = {
     "csr2seg_Cmajor": (None, [c_int] + [c_void_p] * 3 + [c_int] * 3 + [c_void_p] * 4 + [c_int, c_void_p]),
     "dfs": (None, [c_void_p] * 4 + [c_int] * 3),
     "gorder": (None, [c_void_p] * 4 + [c_int] * 3),
+    "rabbit": (None, [c_void_p] * 4 + [c_int] * 3),
     "perm_apply": (None, [c_void_p] * 4 + [c_int] * 3),
     "permutate": (None, [c_void_p] * 3 + [c_int] * 3),
 }

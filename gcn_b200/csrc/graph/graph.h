@@ -49,6 +49,10 @@ void perm_apply(int32_t* rowptr, int32_t* col, float* val, const int32_t* vomp, 
 // DFS pre-order from vertex 0, restart at lowest unvisited (renumber.cu:56-95): vomp[new]=old
 void dfs_order(const CsrView& g, int32_t* vomp);
 
+// Rabbit order (renumber.cu:319-522: iterative modularity agglomeration, dendrogram leaf order,
+// hub grouping off): vomp[new] = old
+void rabbit_order(const CsrView& g, int32_t* vomp);
+
 // Reference tile format (tile.cu:11-169)
 struct TileOut {
   int32_t* segVoMap;         // [tm * n_segs]        may be null (count only)

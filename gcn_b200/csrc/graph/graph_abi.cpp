@@ -133,6 +133,16 @@ int gcnb_renumber_dfs(int32_t* rowptr, int32_t* col, float* val, int32_t* vomp, 
   return GCNB_OK;
 }
 
+int gcnb_renumber_rabbit(int32_t* rowptr, int32_t* col, float* val, int32_t* vomp, int64_t m,
+                         int64_t nnz) {
+  int rc = check_csr(rowptr, col, m, nnz);
+  if (rc != GCNB_OK) return rc;
+  GCNB_REQUIRE(vomp != nullptr || m == 0, "vomp is null");
+  rabbit_order({rowptr, col, m, nnz}, vomp);
+  perm_apply(rowptr, col, val, vomp, m, nnz);
+  return GCNB_OK;
+}
+
 int gcnb_tile_count(const int32_t* rowptr, const int32_t* col, int64_t m, int64_t nnz, int tm,
                     int64_t* n_segs_out) {
   GCNB_REQUIRE(rowptr && (nnz == 0 || col) && n_segs_out, "null pointer");
@@ -170,6 +180,11 @@ static void report(const char* fn, int rc) {
 void dfs(int* rowPtr, int* col, float* vals, int* vomp, int m, int n, int nnz) {
   (void)n;
   report("dfs", gcnb_renumber_dfs(rowPtr, col, vals, vomp, m, nnz));
+}
+
+void rabbit(int* rowPtr, int* col, float* vals, int* vomp, int m, int n, int nnz) {
+  (void)n;
+  report("rabbit", gcnb_renumber_rabbit(rowPtr, col, vals, vomp, m, nnz));
 }
 
 void gorder(int* rowPtr, int* col, float* vals, int* vomp, int m, int n, int nnz) {

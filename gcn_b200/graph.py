@@ -83,6 +83,11 @@ def renumber_dfs(rowptr, col, val):
     return _renumber("gcnb_renumber_dfs", rowptr, col, val)
 
 
+def renumber_rabbit(rowptr, col, val):
+    """rabbit() of the reference (renumber.cu:319-522), its default order (RBT, gcn6.py:27-30)."""
+    return _renumber("gcnb_renumber_rabbit", rowptr, col, val)
+
+
 def renumber_rcm(rowptr, col, val):
     return _renumber("gcnb_renumber_rcm", rowptr, col, val)
 

@@ -6,7 +6,7 @@ names and defaults, Adam(lr, weight_decay) over all parameters, NLL loss on ``id
 three training loops (without validation / with validation / early stopping), and the per-dataset
 layer-2 choice (A·(XW) for pubmed/flickr, (A·X)·W otherwise, gcn5.py:160-163).  Changed on purpose:
 
-  * ``fit`` accepts an optional vertex reordering (``reorder='gorder'|'rcm'|'deg'|'dfs'|None``,
+  * ``fit`` accepts an optional vertex reordering (``reorder='rabbit'|'gorder'|'rcm'|'deg'|'dfs'|None``,
     the module constants OVO/DFS/GOR/RBT of gcn6.py:27-30): Â is renumbered on the host
     (bit-exact with the reference's renumber.cu), features AND labels AND index sets are permuted
     consistently (the reference permutes idx_train but not the labels, SURVEY.md §4 defect 2).
@@ -146,7 +146,7 @@ class GCN(nn.Module):
             vomp = None
             rp, ci, va = mx.indptr, mx.indices, mx.data
             if reorder:
-                fn = {"gorder": graph.renumber_gorder, "rcm": graph.renumber_rcm,
+                fn = {"gorder": graph.renumber_gorder, "rcm": graph.renumber_rcm, "rabbit": graph.renumber_rabbit,
                       "deg": graph.renumber_deg, "dfs": graph.renumber_dfs}[reorder]
                 rp, ci, va, vomp = fn(rp, ci, va)
             plan = ops.SpmmPlan(rp, ci, va, mx.shape, device=self.device)

@@ -158,6 +158,11 @@ int gcnb_renumber_gorder(int32_t* rowptr, int32_t* col, float* val, int32_t* vom
                          int64_t nnz, int window);
 int gcnb_renumber_dfs(int32_t* rowptr, int32_t* col, float* val, int32_t* vomp, int64_t m,
                       int64_t nnz);
+/* rabbit() renumber.cu:319-522 — the reference's default order (RBT = 1, pygcn/gcn6.py:27-30):
+ * iterative modularity agglomeration (opt_iterative, shyness 1, hub grouping off), vertices laid out
+ * by dendrogram leaf order; CSR rewritten in place, vomp[new] = old. */
+int gcnb_renumber_rabbit(int32_t* rowptr, int32_t* col, float* val, int32_t* vomp, int64_t m,
+                         int64_t nnz);
 int gcnb_renumber_rcm(int32_t* rowptr, int32_t* col, float* val, int32_t* vomp, int64_t m,
                       int64_t nnz);
 int gcnb_renumber_deg(int32_t* rowptr, int32_t* col, float* val, int32_t* vomp, int64_t m,
@@ -195,8 +200,9 @@ void csr2tile(int* rowPtr, int* col, float* vals, int m, int n, int nnz, int* vo
 void csr2seg_Cmajor(int ridx, int* rowPtr, int* colIdx, float* vals, int m, int n, int nnz,
                     int* voMp, int* segVoMap, int* seg_rowPtr, float* segNzCV, int tm,
                     int* n_segs);
-/* renumber.cu:23,157,233 — host pointers, CSR rewritten in place */
+/* renumber.cu:23,157,233,319 — host pointers, CSR rewritten in place */
 void dfs(int* rowPtr, int* col, float* vals, int* vomp, int m, int n, int nnz);
+void rabbit(int* rowPtr, int* col, float* vals, int* vomp, int m, int n, int nnz);
 void gorder(int* rowPtr, int* col, float* vals, int* vomp, int m, int n, int nnz);
 void perm_apply(int* rowPtr, int* col, float* vals, int* vomp, int m, int n, int nnz);
 /* permutate.cu:40-41 — device pointers, in place (through plan-free scratch), labels untouched */

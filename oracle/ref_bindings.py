@@ -60,6 +60,10 @@ def ref_gorder(rowptr, col, val):
     return _renumber("gorder", rowptr, col, val)
 
 
+def ref_rabbit(rowptr, col, val):
+    return _renumber("rabbit", rowptr, col, val)
+
+
 def ref_perm_apply(rowptr, col, val, vomp):
     return _renumber("perm_apply", rowptr, col, val, vomp)[:3]
 

@@ -92,7 +92,7 @@ def graph_case(name, kind, n, e, k, seed):
     out["rank_rcm"] = R.ref_order_rcm(rp, ci)
     out["rank_gorder3"] = R.ref_order_gorder(rp, ci, 3)
     out["rank_gorder5"] = R.ref_order_gorder(rp, ci, 5)
-    for nm, fn in (("gorder", R.ref_gorder), ("dfs", R.ref_dfs)):
+    for nm, fn in (("gorder", R.ref_gorder), ("dfs", R.ref_dfs), ("rabbit", R.ref_rabbit)):
         r2, c2, v2, vomp = fn(rp, ci, va)
         out[f"{nm}_rowptr"], out[f"{nm}_col"], out[f"{nm}_val"], out[f"{nm}_vomp"] = r2, c2, v2, vomp
     perm = rng.permutation(n).astype(np.int32)

@@ -23,7 +23,8 @@ def test_orders_bit_exact(golden_graph):
 def test_renumber_bit_exact(golden_graph):
     g = golden_graph
     rp, ci, va = g["rowptr"], g["col"], g["val"]
-    for nm, fn in (("gorder", graph.renumber_gorder), ("dfs", graph.renumber_dfs)):
+    for nm, fn in (("gorder", graph.renumber_gorder), ("dfs", graph.renumber_dfs),
+                   ("rabbit", graph.renumber_rabbit)):
         r2, c2, v2, vomp = fn(rp, ci, va)
         assert np.array_equal(vomp, g[f"{nm}_vomp"]), nm
         assert np.array_equal(r2, g[f"{nm}_rowptr"]) and np.array_equal(c2, g[f"{nm}_col"])
@@ -85,8 +86,16 @@ def test_vs_compiled_reference_random(seed, capfd):
     assert np.array_equal(graph.order_rcm(rp, ci), R.ref_order_rcm(rp, ci))
     for w in (1, 3, 7):
         assert np.array_equal(graph.order_gorder(rp, ci, w), R.ref_order_gorder(rp, ci, w))
-    for ours, ref in ((graph.renumber_gorder, R.ref_gorder), (graph.renumber_dfs, R.ref_dfs)):
+    for ours, ref in ((graph.renumber_gorder, R.ref_gorder), (graph.renumber_dfs, R.ref_dfs),
+                      (graph.renumber_rabbit, R.ref_rabbit)):
         assert all(np.array_equal(x, y) for x, y in zip(ours(rp, ci, va), ref(rp, ci, va)))
+    # Rabbit on asymmetric patterns (its degree bookkeeping depends on the direction, renumber.cu:383-399)
+    import scipy.sparse as sp
+    for tri in (sp.triu, sp.tril):
+        T = tri(A).tocsr()
+        T.sort_indices()
+        assert all(np.array_equal(x, y) for x, y in zip(graph.renumber_rabbit(T.indptr, T.indices, T.data),
+                                                        R.ref_rabbit(T.indptr, T.indices, T.data)))
     t, r = graph.csr2tile(rp, ci, va), R.ref_csr2seg(rp, ci, va)
     for key in ("n_segs", "segVoMap", "seg_rowPtr", "segNzCV"):
         assert np.array_equal(t[key], r[key]), key
@@ -139,6 +148,9 @@ def test_compat_shim_host_entry_points(golden_graph):
     rp, ci, va = g["rowptr"].copy(), g["col"].copy(), g["val"].copy()
     _ffi.lib.dfs(p(rp), p(ci), p(va), p(vomp), m, m, nnz)
     assert np.array_equal(vomp, g["dfs_vomp"]) and np.array_equal(rp, g["dfs_rowptr"])
+    rp, ci, va = g["rowptr"].copy(), g["col"].copy(), g["val"].copy()
+    _ffi.lib.rabbit(p(rp), p(ci), p(va), p(vomp), m, m, nnz)     # renumber.cu:319, the reference's default order
+    assert np.array_equal(vomp, g["rabbit_vomp"]) and np.array_equal(ci, g["rabbit_col"])
     # csr2seg_Cmajor panel by panel, like csr2tile's loop (tile.cu:109-113)
     rp, ci, va = g["rowptr"], g["col"], g["val"]
     ns = int(g["tile_n_segs"])

@@ -66,7 +66,7 @@ def test_layer_api_matches_reference_signature(golden_gcn):
     assert l2.bias is None and rel_err(out2.detach().cpu().numpy(), ref2.detach().cpu().numpy()) < 1e-4
 
 
-@pytest.mark.parametrize("reorder", [None, "gorder", "rcm"])
+@pytest.mark.parametrize("reorder", [None, "gorder", "rcm", "rabbit"])
 def test_fit_trains_and_reorder_is_consistent(golden_gcn, reorder):
     g = golden_gcn
     n, a, feats = _load(g)
