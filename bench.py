@@ -63,6 +63,9 @@ def parse():
     ap.add_argument("--assoc", default="auto", choices=["auto", "reference"],
                     help="epoch mode: 'reference' = gc1 Â·(X·W1), gc2 (Â·H)·W2 as pygcn/gcn5.py builds them; 'auto' = "
                          "the same layers evaluated at the narrower SpMM width with Â·X cached (gcn_b200/model.py)")
+    ap.add_argument("--perm-file", default="",
+                    help="apply a cached vertex permutation (.npy int32 vomp[new] = old, e.g. a Gorder result "
+                         "computed once on the host) instead of computing --order in this run")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -172,10 +175,22 @@ def make_workload(args, device):
                                          edge_factor=args.edge_factor, shuffle=args.shuffle)
         name = f"rmat-s{args.scale}-ef{args.edge_factor}"
     else:
-        rp, ci, va, n = synth.make_graph(args.workload, device=device, shuffle=args.shuffle)
+        # a cached permutation belongs to ONE graph: torch's CPU and CUDA generators differ, so with
+        # --perm-file the graph is generated on the CPU like the run that produced the file did
+        gen_dev = "cpu" if args.perm_file else device
+        rp, ci, va, n = synth.make_graph(args.workload, device=gen_dev, shuffle=args.shuffle)
         name = f"{args.workload}-shaped"
     args.reorder_s = None
-    if args.order != "none":
+    if args.perm_file:
+        from gcn_b200 import graph
+        vomp = np.load(args.perm_file).astype(np.int32)
+        if sorted(vomp.tolist()) != list(range(n)):
+            raise SystemExit(f"{args.perm_file} is not a permutation of {n} vertices")
+        t0 = time.perf_counter()
+        rp, ci, va = graph.perm_apply(rp, ci, va, vomp)
+        args.reorder_s = round(time.perf_counter() - t0, 2)
+        args.order = f"cached {os.path.basename(args.perm_file)}; applying it took"
+    elif args.order != "none":
         # host preprocessing of the path (renumber.cu / order_*.cu equivalents, bit-exact): timed,
         # reported, outside the SpMM step
         from gcn_b200 import graph

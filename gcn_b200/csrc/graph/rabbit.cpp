@@ -3,8 +3,9 @@
 // opt_iterative = true, hub grouping off, shyness 1).
 //
 // Written from the behaviour of the reference so that vomp is bit-exact with it, but on flat data:
-// the per-cluster neighbour weights are sorted (key, weight) vectors instead of one std::map per
-// vertex, the dendrogram is two index arrays instead of pointer nodes (and is walked iteratively —
+// the per-cluster neighbour weights are open-addressing hash tables instead of one std::map per
+// vertex (merging into a hub is O(1) per edge; on the Reddit-shaped graph sorted vectors were
+// quadratic), the dendrogram is two index arrays instead of pointer nodes (and is walked iteratively —
 // the reference recurses, which overflows the stack on path-like merges), degrees and rounds are
 // plain arrays.  What has to match exactly for the permutation to match:
 //   * a cluster's neighbours are visited in ascending id and the FIRST strict maximum of
@@ -26,28 +27,86 @@ namespace graph {
 
 namespace {
 
-using Entry = std::pair<int32_t, int32_t>;   // (neighbour cluster, accumulated weight)
-using Row = std::vector<Entry>;
+// Neighbour weights of one cluster: open-addressing hash table (linear probing, backward-shift
+// deletion, power-of-two capacity, load <= 1/2).  The reference keeps a std::map per vertex and so
+// visits neighbours in ascending id; the only place where the order is observable is the choice of
+// the merge target — "first strict maximum in ascending id" — which is the same as "maximum, ties to
+// the smallest id" and needs no order.  Everything else adds integers, which commutes.
+struct Table {
+  std::vector<int32_t> key, val;   // key < 0: empty slot
+  int32_t count = 0;
+  uint32_t mask = 0;
 
-inline Row::iterator find_key(Row& r, int32_t key) {
-  return std::lower_bound(r.begin(), r.end(), key,
-                          [](const Entry& e, int32_t k) { return e.first < k; });
-}
-
-// r[key] += w (inserting the key when absent), keeping r sorted
-inline void add_weight(Row& r, int32_t key, int32_t w) {
-  auto it = find_key(r, key);
-  if (it != r.end() && it->first == key) it->second += w;
-  else r.insert(it, Entry(key, w));
-}
+  static uint32_t hash(int32_t k) { return (uint32_t)k * 2654435761u; }
+  void init(int32_t expected) {
+    uint32_t cap = 4;
+    while (cap < 2u * (uint32_t)expected + 2u) cap <<= 1;
+    key.assign(cap, -1);
+    val.assign(cap, 0);
+    mask = cap - 1;
+    count = 0;
+  }
+  void grow() {
+    std::vector<int32_t> ok, ov;
+    ok.swap(key);
+    ov.swap(val);
+    const uint32_t cap = (uint32_t)ok.size() * 2;
+    key.assign(cap, -1);
+    val.assign(cap, 0);
+    mask = cap - 1;
+    count = 0;
+    for (size_t i = 0; i < ok.size(); ++i)
+      if (ok[i] >= 0) add(ok[i], ov[i]);
+  }
+  int32_t* find(int32_t k) {
+    for (uint32_t i = hash(k) & mask;; i = (i + 1) & mask) {
+      if (key[i] == k) return &val[i];
+      if (key[i] < 0) return nullptr;
+    }
+  }
+  void add(int32_t k, int32_t w) {   // table[k] += w
+    if (2u * (uint32_t)(count + 1) > mask + 1) grow();
+    for (uint32_t i = hash(k) & mask;; i = (i + 1) & mask) {
+      if (key[i] == k) { val[i] += w; return; }
+      if (key[i] < 0) { key[i] = k; val[i] = w; ++count; return; }
+    }
+  }
+  bool erase(int32_t k, int32_t* w_out) {
+    uint32_t i = hash(k) & mask;
+    for (;; i = (i + 1) & mask) {
+      if (key[i] == k) break;
+      if (key[i] < 0) return false;
+    }
+    *w_out = val[i];
+    // backward-shift deletion keeps every probe sequence gap-free
+    for (uint32_t j = (i + 1) & mask;; j = (j + 1) & mask) {
+      if (key[j] < 0) break;
+      const uint32_t home = hash(key[j]) & mask;
+      if (((j - home) & mask) >= ((j - i) & mask)) {
+        key[i] = key[j];
+        val[i] = val[j];
+        i = j;
+      }
+    }
+    key[i] = -1;
+    --count;
+    return true;
+  }
+  void release() {
+    std::vector<int32_t>().swap(key);
+    std::vector<int32_t>().swap(val);
+    count = 0;
+    mask = 0;
+  }
+};
 
 }  // namespace
 
 void rabbit_order(const CsrView& g, int32_t* vomp) {
   const int64_t n = g.m;
   if (n == 0) return;
-  // undirected unit-weight neighbour lists without self loops
-  std::vector<Row> nbr((size_t)n);
+  // undirected unit-weight neighbour tables without self loops
+  std::vector<Table> nbr((size_t)n);
   std::vector<int32_t> deg((size_t)n, 0);
   {
     std::vector<int32_t> cnt((size_t)n, 0);
@@ -56,28 +115,23 @@ void rabbit_order(const CsrView& g, int32_t* vomp) {
         const int32_t d = g.col[z];
         if (d != v) { ++cnt[(size_t)v]; ++cnt[(size_t)d]; }
       }
-    for (int64_t v = 0; v < n; ++v) nbr[(size_t)v].reserve((size_t)cnt[(size_t)v]);
+    for (int64_t v = 0; v < n; ++v) nbr[(size_t)v].init(cnt[(size_t)v]);
     for (int64_t v = 0; v < n; ++v)
       for (int64_t z = g.rowptr[v]; z < g.rowptr[v + 1]; ++z) {
         const int32_t d = g.col[z];
         if (d == v) continue;
-        nbr[(size_t)v].emplace_back(d, 1);
-        nbr[(size_t)d].emplace_back((int32_t)v, 1);
+        if (!nbr[(size_t)v].find(d)) nbr[(size_t)v].add(d, 1);
+        if (!nbr[(size_t)d].find((int32_t)v)) nbr[(size_t)d].add((int32_t)v, 1);
       }
-    for (int64_t v = 0; v < n; ++v) {
-      Row& r = nbr[(size_t)v];
-      std::sort(r.begin(), r.end());
-      r.erase(std::unique(r.begin(), r.end(), [](const Entry& a, const Entry& b) { return a.first == b.first; }),
-              r.end());
-    }
     // degree as the reference sees it while it initialises vertex v: out-neighbours of v plus the
     // in-neighbours that were initialised before it
     std::vector<uint8_t> is_out((size_t)n, 0);
     for (int64_t v = 0; v < n; ++v) {
       for (int64_t z = g.rowptr[v]; z < g.rowptr[v + 1]; ++z) is_out[(size_t)g.col[z]] = 1;
       int32_t dv = 0;
-      for (const Entry& e : nbr[(size_t)v])
-        if (is_out[(size_t)e.first] || e.first < v) ++dv;
+      const Table& t = nbr[(size_t)v];
+      for (size_t i = 0; i < t.key.size(); ++i)
+        if (t.key[i] >= 0 && (is_out[(size_t)t.key[i]] || t.key[i] < v)) ++dv;
       deg[(size_t)v] = dv;
       for (int64_t z = g.rowptr[v]; z < g.rowptr[v + 1]; ++z) is_out[(size_t)g.col[z]] = 0;
     }
@@ -101,39 +155,40 @@ void rabbit_order(const CsrView& g, int32_t* vomp) {
               [&](uint32_t a, uint32_t b) { return deg[a] < deg[b]; });
     for (const uint32_t u : cur) {
       if (round_of[u] == round) continue;   // u absorbed somebody this round: it waits for the next
-      Row& ru = nbr[u];
+      Table& ru = nbr[u];
       double best = -1;
       int32_t v = -1;
       const double dv_2m = deg[u] * two_m_inv;
-      for (const Entry& e : ru) {
-        const double dq = e.second - deg[(size_t)e.first] * dv_2m;
-        if (dq > best) { best = dq; v = e.first; }
+      for (size_t i = 0; i < ru.key.size(); ++i) {
+        const int32_t d = ru.key[i];
+        if (d < 0) continue;
+        const double dq = ru.val[i] - deg[(size_t)d] * dv_2m;
+        // first strict maximum in ascending id == maximum with ties to the smallest id
+        if (dq > best || (dq == best && v >= 0 && d < v)) { best = dq; v = d; }
       }
       if (best <= 0) continue;
 
       // u joins v
       deg[(size_t)v] += deg[u];
-      Row& rv = nbr[(size_t)v];
-      for (const Entry& e : ru) {
-        const int32_t d = e.first;
-        if (d == v) continue;
-        add_weight(rv, d, e.second);
-        Row& rd = nbr[(size_t)d];
-        auto it = find_key(rd, (int32_t)u);
-        if (it == rd.end() || it->first != (int32_t)u) continue;
-        const int32_t w = it->second;
-        rd.erase(it);
-        add_weight(rd, v, w);
+      Table& rv = nbr[(size_t)v];
+      for (size_t i = 0; i < ru.key.size(); ++i) {
+        const int32_t d = ru.key[i];
+        if (d < 0 || d == v) continue;
+        rv.add(d, ru.val[i]);
+        Table& rd = nbr[(size_t)d];
+        int32_t w = 0;
+        if (!rd.erase((int32_t)u, &w)) continue;
+        rd.add(v, w);
       }
       {
-        auto it = find_key(rv, (int32_t)u);
-        if (it != rv.end() && it->first == (int32_t)u) rv.erase(it);
+        int32_t w = 0;
+        rv.erase((int32_t)u, &w);
       }
       left[u] = tree[(size_t)v];
       right[u] = tree[u];
       tree[u] = -1;
       tree[(size_t)v] = (int32_t)(n + u);
-      Row().swap(ru);   // never read again
+      ru.release();   // never read again
 
       if (round_of[(size_t)v] == round) continue;
       round_of[(size_t)v] = round;
