@@ -79,7 +79,7 @@ class _XW(torch.autograd.Function):
     def backward(ctx, g):
         X, W, out = ctx.saved_tensors
         if ctx.relu:
-            g = g * (out > 0)
+            g = torch.ops.aten.threshold_backward(g, out, 0.0)   # one pass: g where out > 0 else 0
         g = g.to(torch.float32)
         gX = gW = gb = None
         if ctx.needs_input_grad[0]:

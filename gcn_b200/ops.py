@@ -253,7 +253,7 @@ class _SpMM(torch.autograd.Function):
         g = grad_out
         if ctx.relu:
             (out,) = ctx.saved_tensors
-            g = g * (out > 0)
+            g = torch.ops.aten.threshold_backward(g, out, 0.0)   # one pass: g where out > 0 else 0
         g = g.to(torch.float32)
         grad_B = grad_bias = None
         if ctx.needs_input_grad[1]:
