@@ -66,6 +66,8 @@ def parse():
     ap.add_argument("--perm-file", default="",
                     help="apply a cached vertex permutation (.npy int32 vomp[new] = old, e.g. a Gorder result "
                          "computed once on the host) instead of computing --order in this run")
+    ap.add_argument("--cuda-graph", action="store_true",
+                    help="epoch mode, 1 GPU: replay the training step from a CUDA graph (model.GCN.graphed_step)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -379,7 +381,7 @@ def epoch_line(args, name, n, nnz, world, ms_avg, ms_med, ms_min, clocks, extra)
            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
            "config": {"workload": f"{name} 2-layer GCN {nfeat}->{nhid}->{nclass} training epoch "
                                   "(forward, NLL on 5 % of the vertices, backward, Adam); pygcn/gcn5.py:146-262",
-                      "association": args.assoc,
+                      "association": args.assoc, "cuda_graph": bool(getattr(args, "cuda_graph", False)),
                       "n": n, "nnz": nnz, "l2": "operands >> L2; no flush needed"},
            "ms_median": ms_med, "ms_min": ms_min, "clocks": clocks, "e2e": None}
     out.update(extra)
@@ -402,9 +404,14 @@ def run_epoch_single(args):
     torch.manual_seed(15)
     net = gmodel.GCN(nfeat, nhid, nclass, dataset=args.workload, device=device, association=args.assoc)
     net.features, net.adj_norm, net.labels = X, plan, labels
-    opt = torch.optim.Adam(net.parameters(), lr=net.lr, weight_decay=net.weight_decay)
+    if args.cuda_graph:
+        opt = torch.optim.Adam(net.parameters(), lr=net.lr, weight_decay=net.weight_decay, capturable=True)
+        step = net.graphed_step(opt, labels, idx_train, warmup=3)
+    else:
+        opt = torch.optim.Adam(net.parameters(), lr=net.lr, weight_decay=net.weight_decay)
+        step = lambda: net._step(opt, labels, idx_train)   # noqa: E731
     with ClockSampler(0) as clk:
-        ms_avg, ms_med, ms_min = time_steps(lambda: net._step(opt, labels, idx_train), args.steps, args.warmup, device)
+        ms_avg, ms_med, ms_min = time_steps(step, args.steps, args.warmup, device)
     print(json.dumps(epoch_line(args, name, n, nnz, 1, ms_avg, ms_med, ms_min, clk.summary(),
                                 {"gpu_launches": None, "note": ("2 SpMMs (width nclass) + 6 tcgen05 GEMMs of ours per epoch, Â·X cached; "
                                                                 if args.assoc == "auto" else "4 SpMMs + 6 tcgen05 GEMMs of ours per epoch; ")

@@ -188,7 +188,7 @@ class GCN(nn.Module):
         return idx.to(self.device)
 
     def fit(self, features, adj, labels, idx_train, idx_val=None, train_iters=200, initialize=True,
-            verbose=False, normalize=True, patience=500, name="dataset", reorder=None):
+            verbose=False, normalize=True, patience=500, name="dataset", reorder=None, cuda_graph=False):
         self.device = self.gc1.weight.device
         if self.device.type != "cuda":
             raise RuntimeError("gcn_b200: GCN must live on a CUDA device (no CPU fallback)")
@@ -200,7 +200,7 @@ class GCN(nn.Module):
         idx_train = self._map_index(idx_train)
         idx_val = self._map_index(idx_val)
         if idx_val is None:
-            self._train_without_val(self.labels, idx_train, train_iters, verbose)
+            self._train_without_val(self.labels, idx_train, train_iters, verbose, cuda_graph=cuda_graph)
         elif patience < train_iters:
             self._train_with_early_stopping(self.labels, idx_train, idx_val, train_iters, patience, verbose)
         else:
@@ -215,7 +215,46 @@ class GCN(nn.Module):
         optimizer.step()
         return output, loss
 
-    def _train_without_val(self, labels, idx_train, train_iters, verbose):
+    def graphed_step(self, optimizer, labels, idx_train, warmup=3):
+        """One training step (forward, NLL, backward, optimizer) captured in a CUDA graph.
+
+        The epoch of a small graph is launch-bound (Cora-shaped: ~60 kernels, 1.4 ms eager); the
+        kernels of libgcn_b200.so take torch's current stream and use only stream-ordered
+        allocations, so they capture like torch's own.  `optimizer` must be capturable
+        (``Adam(..., capturable=True)``).  `warmup` eager steps run first (they are real training
+        steps).  Returns ``replay() -> (output, loss)``: static tensors refreshed by every replay."""
+        side = torch.cuda.Stream(self.device)
+        side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(side):
+            for _ in range(warmup):
+                self._step(optimizer, labels, idx_train)
+        torch.cuda.current_stream(self.device).wait_stream(side)
+        optimizer.zero_grad(set_to_none=True)
+        graph_ = torch.cuda.CUDAGraph()
+        self.train()
+        with torch.cuda.graph(graph_):
+            output = self.forward(self.features, self.adj_norm)
+            loss = F.nll_loss(output[idx_train], labels[idx_train])
+            loss.backward()
+            optimizer.step()
+
+        def replay():
+            graph_.replay()
+            return output, loss
+        replay.graph = graph_
+        return replay
+
+    def _train_without_val(self, labels, idx_train, train_iters, verbose, cuda_graph=False):
+        if cuda_graph and train_iters > 3:
+            optimizer = optim.Adam(self.parameters(), lr=self.lr, weight_decay=self.weight_decay, capturable=True)
+            replay = self.graphed_step(optimizer, labels, idx_train, warmup=3)
+            output = None
+            for i in range(3, train_iters):
+                output, loss = replay()
+                if verbose and i % 10 == 0:
+                    print(f"Epoch {i:3d}, training loss: {loss.item():.6f}")
+            self.output = output
+            return
         optimizer = optim.Adam(self.parameters(), lr=self.lr, weight_decay=self.weight_decay)
         output = None
         for i in range(train_iters):

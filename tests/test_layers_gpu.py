@@ -118,3 +118,26 @@ def test_min_width_association_matches_reference_association(golden_gcn, dataset
     assert abs(res["auto"][1] - res["reference"][1]) < 1e-5
     for ga, gr in zip(res["auto"][2], res["reference"][2]):
         assert ga.shape == gr.shape and rel_err(ga, gr) < 5e-5
+
+
+def test_cuda_graph_step_matches_eager(golden_gcn):
+    """The training step replayed from a CUDA graph (every kernel of ours captured on torch's stream)
+    follows the same trajectory as eager steps: dropout off, same seed, same number of steps."""
+    g = golden_gcn
+    n, a, _ = _load(g)
+    rng = np.random.default_rng(5)
+    X = torch.from_numpy(rng.standard_normal((n, 12)).astype(np.float32))
+    labels = rng.integers(0, 7, n)
+    idx = np.arange(0, n, 2)
+    losses = {}
+    for graphed in (False, True):
+        torch.manual_seed(7)
+        m = model.GCN(nfeat=12, nhid=16, nclass=7, dropout=0.0, device=DEV, association="auto")
+        m.fit(X, a, labels, idx, train_iters=12, cuda_graph=graphed)
+        m.eval()
+        with torch.no_grad():
+            out = m.forward(m.features, m.adj_norm)
+        losses[graphed] = (F.nll_loss(out[torch.from_numpy(idx).to(DEV)], m.labels[torch.from_numpy(idx).to(DEV)]).item(),
+                           m.gc1.weight.detach().cpu().numpy())
+    assert abs(losses[True][0] - losses[False][0]) < 1e-4
+    assert rel_err(losses[True][1], losses[False][1]) < 1e-4
