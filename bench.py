@@ -232,9 +232,53 @@ def cpu_reference_sample(rp, ci, va, n, k, budget_s=10.0, reps=1):
     return gflops, torch.get_num_threads(), sample, best
 
 
+def run_reference_epoch(args):
+    """--impl reference --mode epoch: the reference's 2-layer GCN epoch on the host cores (torch CPU ops,
+    pygcn/gcn1.py:62-118, :176-203, restated in oracle/spmm_oracle.py gcn_epoch_cpu), whole graph —
+    only for the shapes where that takes seconds (Cora- and arxiv-shaped)."""
+    name, rp, ci, va, n, _ = make_workload(args, "cuda" if torch.cuda.is_available() else "cpu")
+    nnz = int(rp[-1])
+    nfeat, nhid, nclass = EPOCH_SHAPES[args.workload]
+    base = {"impl": "reference", "metric": "gcn_epoch_ms", "unit": "ms", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "higher_is_better": False, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{name} 2-layer GCN {nfeat}->{nhid}->{nclass} training epoch "
+                                   "(forward, NLL on 5 % of the vertices, backward, Adam); pygcn/gcn1.py:62-203",
+                       "n": n, "nnz": nnz}}
+    if nnz > 5_000_000:
+        base["unavailable"] = "CPU epoch only for the Cora- and arxiv-shaped graphs (bounded run time); use --mode spmm"
+        print(json.dumps(base))
+        return
+    from oracle import spmm_oracle as SO
+    adj = SO.torch_coo(rp, ci, va, (n, n))
+    g = torch.Generator().manual_seed(15)
+    x = torch.randn(n, nfeat, generator=g)
+    labels = torch.randint(0, nclass, (n,), generator=g)
+    idx_train = torch.arange(n // 20)
+    params = []
+    for shape in ((nfeat, nhid), (nhid,), (nhid, nclass), (nclass,)):
+        stdv = 1.0 / (shape[-1] ** 0.5)     # reset_parameters, gcn1.py:33-38
+        params.append(((torch.rand(shape, generator=g) * 2 - 1) * stdv).requires_grad_(True))
+    opt = torch.optim.Adam(params, lr=0.01, weight_decay=5e-4)
+    for _ in range(args.warmup):
+        SO.gcn_epoch_cpu(adj, x, labels, idx_train, params, opt)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        SO.gcn_epoch_cpu(adj, x, labels, idx_train, params, opt)
+    ms = (time.perf_counter() - t0) / args.steps * 1e3
+    base.update({"value": ms, "ms_per_step": ms,
+                 "cpu_baseline": {"value": ms, "unit": "ms", "cores": torch.get_num_threads(), "kind": "port",
+                                  "sample": "whole graph, every step a full epoch"},
+                 "e2e": {"value": ms, "unit": "ms", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
+    print(json.dumps(base))
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
+        return
+    if args.mode == "epoch":
+        run_reference_epoch(args)
         return
     name, rp, ci, va, n, k = make_workload(args, "cuda" if torch.cuda.is_available() else "cpu")
     from oracle import spmm_oracle as SO

@@ -120,3 +120,21 @@ def gcn_layer_cpu(adj_coo, x, weight, bias=None):
     support = torch.spmm(x, weight) if x.is_sparse else torch.mm(x, weight)
     out = torch.spmm(adj_coo, support)
     return out + bias if bias is not None else out
+
+
+def gcn_epoch_cpu(adj_coo, x, labels, idx_train, params, optimizer, dropout=0.5):
+    """One training epoch of the reference's 2-layer GCN on the host cores, restated from
+    pygcn/gcn1.py:62-118 (model: gc1 = A·(X·W1)+b1, ReLU, dropout, gc2 = A·(H·W2)+b2, log_softmax) and
+    :176-203 (_train_without_val: zero_grad, forward, nll_loss on idx_train, backward, Adam step).
+    `params` = (W1, b1, W2, b2) leaf tensors the optimizer owns.  Returns the loss tensor."""
+    import torch
+    import torch.nn.functional as F
+    W1, b1, W2, b2 = params
+    optimizer.zero_grad()
+    h = F.relu(gcn_layer_cpu(adj_coo, x, W1, b1))
+    h = F.dropout(h, dropout, training=True)
+    out = F.log_softmax(gcn_layer_cpu(adj_coo, h, W2, b2), dim=1)
+    loss = F.nll_loss(out[idx_train], labels[idx_train])
+    loss.backward()
+    optimizer.step()
+    return loss

@@ -54,3 +54,15 @@ def test_kernel_launch_count_follows_the_dispatch():
     assert bench.kernel_launches_per_spmm(dense, 32, "f32") == 2       # packed stream kernel + reduce
     assert bench.kernel_launches_per_spmm(short, 32, "f32") == 1       # lane-group kernel only
     assert bench.kernel_launches_per_spmm(short, 256, "bf16") == 1
+
+
+def test_reference_epoch_arm_line():
+    r = _run("--impl", "reference", "--mode", "epoch", "--workload", "cora", "--steps", "2", "--warmup", "1")
+    assert r.returncode == 0, r.stderr[-2000:]
+    d = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][0])
+    assert d["impl"] == "reference" and d["metric"] == "gcn_epoch_ms" and d["higher_is_better"] is False
+    assert d["value"] > 0 and d["cpu_baseline"]["kind"] == "port" and "1433->16->7" in d["config"]["workload"]
+    # shapes whose CPU epoch would take minutes are declined, not sampled
+    r = _run("--impl", "reference", "--mode", "epoch", "--workload", "rmat", "--scale", "18", "--edge-factor", "16")
+    d = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][0])
+    assert r.returncode == 0 and "unavailable" in d
