@@ -121,3 +121,82 @@ def test_two_ranks_one_gpu(symmetric, exchange):
         assert p.exitcode == 0
     for rank, err in res:
         assert err < 1e-5, (rank, err)     # north_star: 1e-5 relative, fp32
+
+
+def _gcn_worker(rank, world, port, assoc, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import torch.nn.functional as F
+        from gcn_b200 import dist as gdist
+        from gcn_b200 import model, ops
+
+        class Part(gdist.PartitionedSpMM):
+            def _rank_barrier(self):
+                torch.cuda.synchronize()
+                dist.barrier()
+
+        dev = torch.device("cuda", 0)
+        torch.cuda.set_device(dev)
+        A = random_normalized_graph(900, 9000, 13, "skew")
+        n = A.shape[0]
+        nfeat, nhid, nclass = 12, 16, 7
+        rng = np.random.default_rng(2)
+        X = rng.standard_normal((n, nfeat)).astype(np.float32)
+        y = rng.integers(0, nclass, n)
+        n_train = n // 3
+        part = Part(A.indptr, A.indices, A.data, n, device=dev, exchange="pull")
+        lo, hi = part.lo, part.hi
+        net = gdist.PartitionedGCN(part, nfeat, nhid, nclass, dropout=0.0, association=assoc)
+        # the same model in one process, same initial weights
+        ref = model.GCN(nfeat, nhid, nclass, dropout=0.0, device=dev, association=assoc)
+        with torch.no_grad():
+            for a, b in zip(ref.parameters(), net.parameters()):
+                a.copy_(b)
+        plan = ops.SpmmPlan.from_scipy(A, device=dev)
+        ref.features, ref.adj_norm = torch.from_numpy(X).to(dev), plan
+        labels = torch.from_numpy(y).to(dev)
+        opt = torch.optim.Adam(ref.parameters(), lr=0.01, weight_decay=5e-4)
+        idx = torch.arange(n_train, device=dev)
+        Xl = torch.from_numpy(X[lo:hi].copy()).to(dev)
+        idx_l = torch.arange(max(0, min(hi, n_train) - lo), device=dev)
+        errs = []
+        for _ in range(3):
+            net.train()
+            out_l = net.forward(Xl).detach()
+            ref.train()
+            out_f = ref.forward(ref.features, plan).detach()
+            errs.append(rel_err(out_l.cpu().numpy(), out_f[lo:hi].cpu().numpy()))
+            loss_l = net.step(Xl, labels[lo:hi], idx_l, n_train)
+            _, loss_f = ref._step(opt, labels, idx)
+            tot = loss_l.detach().clone()
+            dist.all_reduce(tot)           # local contributions sum to the global mean loss
+            errs.append(abs(tot.item() - loss_f.item()))
+            for a, b in zip(ref.parameters(), net.parameters()):
+                errs.append(rel_err(b.detach().cpu().numpy(), a.detach().cpu().numpy()))
+        torch.cuda.synchronize()
+        dist.barrier()
+        part.close()
+        q.put((rank, max(errs)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("assoc", ["reference", "auto"])
+def test_partitioned_gcn_matches_single_process(assoc):
+    """Two ranks (one GPU, pull exchange): forward rows, loss and the weights after each of three Adam
+    steps equal those of gcn_b200.model.GCN run in one process with the same initial weights."""
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_gcn_worker, args=(r, world, port, assoc, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=300) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, err in res:
+        assert err < 2e-4, (rank, err)
