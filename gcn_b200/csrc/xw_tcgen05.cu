@@ -28,6 +28,8 @@
 //     covers the tall-K product dW = X^T·dS.
 #include <cuda_bf16.h>
 
+#include <stdlib.h>
+
 #include <algorithm>
 
 #include "common.h"
@@ -417,6 +419,7 @@ int launch_bn(int bn, const xw::Params& p, int64_t tiles, int splits, cudaStream
     case 16: return launch_main<16, MODE>(p, tiles, splits, stream);
     case 32: return launch_main<32, MODE>(p, tiles, splits, stream);
     case 64: return launch_main<64, MODE>(p, tiles, splits, stream);
+    case 256: return launch_main<256, MODE>(p, tiles, splits, stream);
     default: return launch_main<128, MODE>(p, tiles, splits, stream);
   }
 }
@@ -453,7 +456,11 @@ extern "C" int gcnb_xw(const float* X, int64_t ldx, int trans_x, const float* W,
     return GCNB_OK;
   }
 
-  const int bn = N <= 16 ? 16 : (N <= 32 ? 32 : (N <= 64 ? 64 : 128));
+  // N > 128: a 256-wide tile would convert X once instead of once per 128-wide n-tile, but its 131 KB of
+  // shared memory leave one 4-warp CTA per SM: measured slower (products epoch 23.3 vs 21.9 ms,
+  // profiles/r01_ae_*), so it stays an experiment switch
+  static const int wide = getenv("GCNB_XW_BN256") ? atoi(getenv("GCNB_XW_BN256")) : 0;
+  const int bn = N <= 16 ? 16 : (N <= 32 ? 32 : (N <= 64 ? 64 : ((N > 128 && wide) ? 256 : 128)));
   const int ntiles = (N + bn - 1) / bn;
   const int nkb = (K + xw::BK - 1) / xw::BK;
   const int64_t mtiles = (M + xw::BM - 1) / xw::BM;
