@@ -5,21 +5,26 @@
 // partial rows; here the matrix stays in (interleaved) CSR, every output element is produced by
 // exactly one warp or one CTA, and nothing is atomic.
 //
-//   rows class  (spmm_rows_kernel)   one lane-group of G lanes per row, 32/G rows per warp.
-//                                    (col,val) pairs are fetched G at a time as one coalesced
-//                                    8-byte-per-lane load and broadcast with __shfl_sync; every
-//                                    lane owns NV vectors (128-bit where alignment allows) of the
-//                                    feature row, so one warp-wide load instruction covers a
-//                                    contiguous run of B.  U independent gathers are in flight per
-//                                    lane before the first FMA.
-//   block class (spmm_block_kernel)  rows with >= kLongRow non-zeros, cut into items of at most
-//                                    kChunk non-zeros.  One CTA per item: the item's (col,val)
-//                                    tile is staged into shared memory with one TMA bulk copy
-//                                    (cp.async.bulk + mbarrier), the 8 warps stride over the
+//   stream class (spmm_stream_kernel)        the default for feature rows wider than 16 vectors: a warp owns
+//                                    a segment of ~768 consecutive non-zeros (whole short rows or a
+//                                    piece of a long row) and streams it through a register ring of
+//                                    in-flight feature-row gathers; (col,val) pairs arrive through a
+//                                    per-warp shared-memory slab.
+//   packed stream (spmm_stream_packed_kernel)  narrow feature rows on matrices with >= 24 nnz/row:
+//                                    the same, with S = 2/4/8 non-zeros fetched per warp-wide load.
+//   rows class  (spmm_rows_kernel)   narrow feature rows on short-row matrices: one lane-group of G
+//                                    lanes per row, 32/G rows per warp.  (col,val) pairs are fetched G
+//                                    at a time as one coalesced 8-byte-per-lane load and broadcast with
+//                                    __shfl_sync; U independent gathers are in flight per lane.
+//   block class (spmm_block_kernel)  companion of the rows class for rows with >= kLongRow non-zeros,
+//                                    cut into items of at most kChunk non-zeros.  One CTA per item: the
+//                                    item's (col,val) tile is staged into shared memory with one TMA
+//                                    bulk copy (cp.async.bulk + mbarrier), the 8 warps stride over the
 //                                    tile, partial rows are combined with warp shuffles and a
-//                                    shared-memory pass in fixed order.  Rows with several items
-//                                    go through a partials buffer and spmm_reduce_kernel — still
-//                                    no atomics, so results are bit-reproducible.
+//                                    shared-memory pass in fixed order.
+//   Rows cut into several pieces go through a partials buffer and spmm_reduce_kernel — still no
+//   atomics, so results are bit-reproducible.  Dispatch: spmm.cu launch_vec; measurements behind every
+//   choice: DESIGN.md §4.
 #pragma once
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
