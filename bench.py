@@ -308,8 +308,11 @@ def run_reference(args):
 
 
 # ---- our arm -------------------------------------------------------------------------------------
-def time_steps(fn, steps, warmup, device, barrier=None):
-    """W untimed + K timed calls; per-step CUDA events on the launching (current) stream."""
+def time_steps(fn, steps, warmup, device, barrier=None, align=None):
+    """W untimed + K timed calls; per-step CUDA events on the launching (current) stream.
+    `align` (N > 1): a stream-ordered rendezvous of the ranks enqueued right before the first event, so
+    that the timed region starts on every GPU when the last rank arrives (a host-side barrier alone
+    leaves the ranks up to a millisecond apart, which the first timed step then absorbs)."""
     for _ in range(warmup):
         fn()
     torch.cuda.synchronize(device)
@@ -319,6 +322,8 @@ def time_steps(fn, steps, warmup, device, barrier=None):
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
     t0 = torch.cuda.Event(enable_timing=True)
     t1 = torch.cuda.Event(enable_timing=True)
+    if align:
+        align()
     t0.record()
     for a, b in ev:
         a.record()
@@ -487,7 +492,7 @@ def run_epoch_multi(args):
 
     with ClockSampler(local) as clk:
         ms_avg, ms_med, ms_min = time_steps(lambda: net.step(X, labels, idx_train, n_train), args.steps,
-                                            args.warmup, device, barrier)
+                                            args.warmup, device, barrier, align=part._rank_barrier)
     t = torch.tensor([ms_avg, ms_med, ms_min], device=device, dtype=torch.float64)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     if rank == 0:
@@ -526,7 +531,8 @@ def run_multi(args):
         dist.barrier(device_ids=[local])
 
     with ClockSampler(local) as clk:
-        ms_avg, ms_med, ms_min = time_steps(lambda: part.forward(B), args.steps, args.warmup, device, barrier)
+        ms_avg, ms_med, ms_min = time_steps(lambda: part.forward(B), args.steps, args.warmup, device, barrier,
+                                            align=part._rank_barrier)
     step_list = time_steps.last
     # the three phases of a step, each timed alone on the compute stream (untimed region of the bench):
     # what the overlap has to hide, and what it cannot
