@@ -382,7 +382,7 @@ def run_single(args):
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": abytes,
-                     "note": "whole-step device time (stream kernel + split-row reduce, 99.8 % / 0.2 % in profiles/r01_x_launches_products_k100.csv) used as the launch duration"},
+                     "note": "whole-step device time (stream kernel + split-row reduce, 99.84 % / 0.16 % of the device time in profiles/r01_ai_launches_products_k100.csv) used as the launch duration"},
         "clocks": clk.summary(),
     }
     traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
