@@ -545,12 +545,40 @@ def run_multi(args):
         holder["full"] = part._exchange(blocks, B, part._prepare(B))
     ph_exch = time_steps(_ex, 5, 2, device, barrier)[1]
     ph_remote = time_steps(lambda: part._mul_remote_accumulate(blocks, holder["full"], out_l), 5, 2, device, barrier)[1]
+    # end to end through the public API (gcn_b200.dist): this rank's rows of B from pinned host memory,
+    # the partitioned SpMM, this rank's rows of C back to pinned host memory, every step
+    e2e_ms, e2e_parts = 0.0, [0.0, 0.0, 0.0]
+    if not args.no_e2e:
+        Bh = torch.randn(part.m_local, k, generator=torch.Generator().manual_seed(15 + rank)).pin_memory()
+        Ch = torch.empty(part.m_local, k).pin_memory()
+        dst = part.next_operand(k) if args.exchange == "pull" else torch.empty(part.m_local, k, device=device)
+
+        def e2e_step():
+            dst.copy_(Bh, non_blocking=True)
+            Ch.copy_(part.forward(dst), non_blocking=True)
+            torch.cuda.synchronize(device)
+        e2e_step()
+        reps = max(3, min(args.steps, 10))
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            e2e_step()
+        barrier()
+        e2e_ms = (time.perf_counter() - t0) / reps * 1e3
+        # where the time goes (this rank, device events): host->device, partitioned SpMM, device->host
+        evs = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        evs[0].record(); dst.copy_(Bh, non_blocking=True)
+        evs[1].record(); out_e = part.forward(dst)
+        evs[2].record(); Ch.copy_(out_e, non_blocking=True)
+        evs[3].record(); torch.cuda.synchronize(device)
+        e2e_parts = [evs[i].elapsed_time(evs[i + 1]) for i in range(3)]
     halo_rows = int(blocks["halo_row"].numel()) if args.exchange == "pull" else (world - 1) * part.stride
-    t = torch.tensor([ms_avg, ms_med, ms_min, ph_local, ph_exch, ph_remote, halo_rows], device=device, dtype=torch.float64)
+    t = torch.tensor([ms_avg, ms_med, ms_min, ph_local, ph_exch, ph_remote, halo_rows, e2e_ms], device=device,
+                     dtype=torch.float64)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     stats = torch.tensor([local_nnz, remote_nnz], device=device, dtype=torch.float64)
     dist.all_reduce(stats, op=dist.ReduceOp.SUM)
-    ms_avg, ms_med, ms_min, ph_local, ph_exch, ph_remote, halo_rows = t.tolist()
+    ms_avg, ms_med, ms_min, ph_local, ph_exch, ph_remote, halo_rows, e2e_ms = t.tolist()
     if rank == 0:
         abytes, flops = synth.spmm_bytes_flops(n, n, nnz, k)
         peak, peak_src = peaks()
@@ -577,7 +605,12 @@ def run_multi(args):
                          "note": "aggregate: algorithmic bytes of the whole SpMM over N x per-GPU HBM peak; "
                                  "the step also moves allgather_bytes over NVLink"},
             "clocks": clk.summary(),
-            "e2e": None,
+            "e2e": None if args.no_e2e else {
+                "value": flops / (e2e_ms * 1e-3) / 1e9, "unit": UNIT, "h2d_bytes_per_step": n * k * 4,
+                "d2h_bytes_per_step": n * k * 4, "ms_per_step": e2e_ms,
+                "rank0_ms_h2d_spmm_d2h": [round(x, 3) for x in e2e_parts],
+                "api": "gcn_b200.dist.PartitionedSpMM.forward per rank, pinned host rows in and out; bytes are "
+                       "the sum over ranks, time the max over ranks (wall clock between barriers)"},
         }))
     dist.destroy_process_group()
 
