@@ -562,9 +562,12 @@ def run_multi(args):
     if not args.no_e2e:
         Bh = torch.randn(part.m_local, k, generator=torch.Generator().manual_seed(15 + rank)).pin_memory()
         Ch = torch.empty(part.m_local, k).pin_memory()
-        dst = part.next_operand(k) if args.exchange == "pull" else torch.empty(part.m_local, k, device=device)
+        dst_ag = None if args.exchange == "pull" else torch.empty(part.m_local, k, device=device)
 
         def e2e_step():
+            # pull mode: the upload lands in the free exchange slot, alternating like any producer does
+            # (a peer may still be pulling the slot of the previous step)
+            dst = part.next_operand(k) if dst_ag is None else dst_ag
             dst.copy_(Bh, non_blocking=True)
             Ch.copy_(part.forward(dst), non_blocking=True)
             torch.cuda.synchronize(device)
@@ -578,6 +581,7 @@ def run_multi(args):
         e2e_ms = (time.perf_counter() - t0) / reps * 1e3
         # where the time goes (this rank, device events): host->device, partitioned SpMM, device->host
         evs = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        dst = part.next_operand(k) if dst_ag is None else dst_ag
         evs[0].record(); dst.copy_(Bh, non_blocking=True)
         evs[1].record(); out_e = part.forward(dst)
         evs[2].record(); Ch.copy_(out_e, non_blocking=True)
