@@ -26,6 +26,10 @@
 //   * Two canonical stages: the MMAs of block i run asynchronously (tcgen05.commit -> mbarrier)
 //     while the CTA converts block i+1.  Split-K (grid.z) with a deterministic two-pass reduction
 //     covers the tall-K product dW = X^T·dS.
+//   * Tall-K variant (BRAW): in dW = X^T·dS BOTH operands are vertex-sized, so an image of the second
+//     one costs a write and a re-read of 8 bytes per element of it (2.5 GB for the products-shaped
+//     layer 1).  There the B operand takes the same road as the A operand: raw rows through a second
+//     cp.async ring, split and transposed into the canonical layout by the thread that fetched them.
 #include <cuda_bf16.h>
 
 #include <stdlib.h>
@@ -46,9 +50,13 @@ constexpr int A_PART = (BK / 4) * A_LBO;   // bytes of one A part (hi or lo), si
 constexpr int RAW_BYTES = BM * BK * 4;
 
 __host__ __device__ constexpr int b_part_bytes(int bn) { return bn * BK * 4; }   // one B part (tf32 sizing)
-__host__ __device__ constexpr int stage_bytes(int bn) { return 2 * A_PART + 2 * b_part_bytes(bn); }
-__host__ __device__ constexpr int smem_bytes(int bn) {
-  return 2 * stage_bytes(bn) + RAW_STAGES * RAW_BYTES + 64;
+// B operand converted in the kernel (BRAW): k-chunk pitch padded like the A tile's, raw ring of its own
+__host__ __device__ constexpr int b_lbo(int bn, bool braw) { return braw ? bn * 16 + 16 : bn * 16; }
+__host__ __device__ constexpr int b_part(int bn, bool braw) { return braw ? (BK / 4) * b_lbo(bn, true) : b_part_bytes(bn); }
+__host__ __device__ constexpr int b_raw_bytes(int bn) { return bn * BK * 4; }
+__host__ __device__ constexpr int stage_bytes(int bn, bool braw = false) { return 2 * A_PART + 2 * b_part(bn, braw); }
+__host__ __device__ constexpr int smem_bytes(int bn, bool braw = false) {
+  return 2 * stage_bytes(bn, braw) + RAW_STAGES * RAW_BYTES + (braw ? RAW_STAGES * b_raw_bytes(bn) : 0) + 64;
 }
 
 // byte offset of element (row, k) inside one operand part; K-major core matrices of 8 rows x 16 B
@@ -117,7 +125,8 @@ __device__ __forceinline__ void cp_async4(uint32_t dst, const void* src, int byt
 
 struct Params {
   const float* X; int64_t ldx; int trans_x;   // op(X) is M x K
-  const uint8_t* w_img;                       // prepared B operand image
+  const uint8_t* w_img;                       // prepared B operand image (null in the BRAW variant)
+  const float* W; int64_t ldw; int w_vec;     // BRAW: raw K x N row-major second operand
   float* D; int64_t ldd;                      // output (or partials when splits > 1)
   int64_t M; int N; int K;
   int nkb;                                    // k-blocks in total
@@ -161,20 +170,23 @@ prep_w_kernel(const float* __restrict__ W, int64_t ldw, int trans_w, int N, int 
 }
 
 // ---- main kernel ---------------------------------------------------------------------------------
-template <int BN, int MODE>
+template <int BN, int MODE, bool BRAW>
 __global__ void __launch_bounds__(THREADS)
 xw_kernel(const Params p) {
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr bool TF32 = MODE != 2;
-  constexpr int B_LBO = BN * 16;
-  constexpr int B_PART = b_part_bytes(BN);
-  constexpr int STAGE = stage_bytes(BN);
+  constexpr int B_LBO = b_lbo(BN, BRAW);
+  constexpr int B_PART = b_part(BN, BRAW);
+  constexpr int STAGE = stage_bytes(BN, BRAW);
+  constexpr int B_RAW = b_raw_bytes(BN);
+  constexpr int NBC = BN * 4;                              // 16-byte chunks of one raw B tile (BK x BN)
   constexpr int B_BYTES = (MODE == 0 ? 2 : 1) * (TF32 ? B_PART : B_PART / 2);  // bytes the MMAs read
   constexpr uint32_t IDESC = make_idesc(TF32 ? 2 : 1, BN);
   constexpr int TMEM_COLS = BN <= 32 ? 32 : (BN <= 64 ? 64 : (BN <= 128 ? 128 : 256));
 
   uint8_t* raw = smem + 2 * STAGE;                         // cp.async ring, thread-private slots
-  uint64_t* bars = reinterpret_cast<uint64_t*>(raw + RAW_STAGES * RAW_BYTES);  // [0,1] mma done, [2,3] B landed
+  uint8_t* braw = raw + RAW_STAGES * RAW_BYTES;            // BRAW: ring of raw B tiles
+  uint64_t* bars = reinterpret_cast<uint64_t*>(braw + (BRAW ? RAW_STAGES * B_RAW : 0));  // [0,1] mma done, [2,3] B landed
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -231,6 +243,27 @@ xw_kernel(const Params p) {
         for (int e = 0; e < 4; ++e) cp_async4(dst + 4 * e, e < valid ? src + e : p.X, e < valid ? 4 : 0);
       }
     }
+    if constexpr (BRAW) {
+      // raw B tile, N-contiguous source: chunk c -> k = c%16, n-chunk c/16 (as the trans_x A tile)
+#pragma unroll
+      for (int j = 0; j < (NBC + THREADS - 1) / THREADS; ++j) {
+        const int c = tid + j * THREADS;
+        if (NBC % THREADS != 0 && c >= NBC) break;
+        const uint32_t dst = smem_addr(braw + slot * B_RAW + c * 16);
+        const int q = k0 + (c & 15);
+        const int n0 = nt * BN + (c >> 4) * 4;
+        const int valid = (q < p.K) ? max(0, min(4, p.N - n0)) : 0;
+        const float* src = p.W + (int64_t)q * p.ldw + n0;
+        if (valid == 0) {
+          cp_async16(dst, p.W, 0);
+        } else if (p.w_vec) {
+          cp_async16(dst, src, valid * 4);
+        } else {
+#pragma unroll
+          for (int e = 0; e < 4; ++e) cp_async4(dst + 4 * e, e < valid ? src + e : p.W, e < valid ? 4 : 0);
+        }
+      }
+    }
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
 
@@ -248,7 +281,7 @@ xw_kernel(const Params p) {
       mbar_wait(smem_addr(bars + s), ((i >> 1) - 1) & 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     }
-    if (tid == 0) {   // B block: one TMA bulk copy of the prepared image
+    if (!BRAW && tid == 0) {   // B block: one TMA bulk copy of the prepared image
       const uint8_t* src = p.w_img + ((int64_t)nt * p.nkb + kb0 + i) * (2 * B_PART);
       const uint32_t bar = smem_addr(bars + 2 + s);
       asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(B_BYTES) : "memory");
@@ -300,6 +333,31 @@ xw_kernel(const Params p) {
         }
       }
     }
+    if constexpr (BRAW) {   // the same for this thread's chunks of the raw B tile (rows of the operand = n)
+      const uint8_t* bslot = braw + (i % RAW_STAGES) * B_RAW;
+      uint8_t* bst = stage + 2 * A_PART;
+#pragma unroll
+      for (int j = 0; j < (NBC + THREADS - 1) / THREADS; ++j) {
+        const int c = tid + j * THREADS;
+        if (NBC % THREADS != 0 && c >= NBC) break;
+        const float4 v = *reinterpret_cast<const float4*>(bslot + c * 16);
+        const float x[4] = {v.x, v.y, v.z, v.w};
+        const int k = c & 15, row0 = (c >> 4) * 4;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          if constexpr (TF32) {
+            const int off = canon_off<4, 4>(row0 + e, k, B_LBO);
+            const uint32_t hi = to_tf32(x[e]);
+            *reinterpret_cast<uint32_t*>(bst + off) = hi;
+            if constexpr (MODE == 0)
+              *reinterpret_cast<uint32_t*>(bst + B_PART + off) = to_tf32(x[e] - __uint_as_float(hi));
+          } else {
+            *reinterpret_cast<__nv_bfloat16*>(bst + canon_off<8, 2>(row0 + e, k, B_LBO)) =
+                __float2bfloat16_rn(x[e]);
+          }
+        }
+      }
+    }
     // refill the ring slot consumed one iteration ago (this thread's own slot: no hazard)
     if (i + RAW_STAGES - 1 < nk) issue_raw(kb0 + i + RAW_STAGES - 1, (i + RAW_STAGES - 1) % RAW_STAGES);
     else asm volatile("cp.async.commit_group;" ::: "memory");
@@ -308,7 +366,7 @@ xw_kernel(const Params p) {
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     if (tid == 0) {
-      mbar_wait(smem_addr(bars + 2 + s), (i >> 1) & 1);    // B block landed
+      if constexpr (!BRAW) mbar_wait(smem_addr(bars + 2 + s), (i >> 1) & 1);    // B block landed
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const uint32_t a_hi = smem_addr(stage), a_lo = a_hi + A_PART;
       const uint32_t b_hi = smem_addr(stage + 2 * A_PART), b_lo = b_hi + (TF32 ? B_PART : 0);
@@ -378,16 +436,26 @@ xw_kernel(const Params p) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(TMEM_COLS) : "memory");
 }
 
-// split-K: D = sum_z partial[z] (+bias)(ReLU), fixed order
-__global__ void __launch_bounds__(256)
+// split-K: D = sum_z partial[z] (+bias)(ReLU), fixed order.  A block owns 32 consecutive output elements;
+// its 8 warps each add every 8th partial (coalesced 128-byte reads), then warp 0 adds the 8 sums in order.
+constexpr int kReduceElems = 32, kReduceLanes = 8;
+__global__ void __launch_bounds__(kReduceElems * kReduceLanes)
 xw_reduce_kernel(const float* __restrict__ part, int splits, int64_t M, int N, float* __restrict__ D,
                  int64_t ldd, const float* __restrict__ bias, int epi) {
-  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= M * N) return;
+  __shared__ float sums[kReduceLanes][kReduceElems];
+  const int e = threadIdx.x % kReduceElems, zl = threadIdx.x / kReduceElems;
+  const int64_t total = M * N;
+  const int64_t idx = (int64_t)blockIdx.x * kReduceElems + e;
+  float v = 0.f;
+  if (idx < total)
+    for (int z = zl; z < splits; z += kReduceLanes) v += part[(int64_t)z * total + idx];
+  sums[zl][e] = v;
+  __syncthreads();
+  if (zl != 0 || idx >= total) return;
+#pragma unroll
+  for (int j = 1; j < kReduceLanes; ++j) v += sums[j][e];
   const int64_t r = idx / N;
   const int c = (int)(idx % N);
-  float v = 0.f;
-  for (int z = 0; z < splits; ++z) v += part[(int64_t)z * M * N + idx];
   if (epi & GCNB_EPI_BIAS) v += __ldg(bias + c);
   if (epi & GCNB_EPI_RELU) v = fmaxf(v, 0.f);
   D[r * ldd + c] = v;
@@ -400,27 +468,36 @@ using namespace gcnb;
 
 namespace {
 
-template <int BN, int MODE>
+template <int BN, int MODE, bool BRAW>
 int launch_main(const xw::Params& p, int64_t tiles, int splits, cudaStream_t stream) {
   static bool configured = false;   // benign race: the attribute is idempotent
   if (!configured) {
-    GCNB_CHECK_CUDA(cudaFuncSetAttribute(xw::xw_kernel<BN, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         xw::smem_bytes(BN)));
+    GCNB_CHECK_CUDA(cudaFuncSetAttribute(xw::xw_kernel<BN, MODE, BRAW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         xw::smem_bytes(BN, BRAW)));
     configured = true;
   }
-  xw::xw_kernel<BN, MODE><<<dim3((unsigned)tiles, (unsigned)splits), xw::THREADS, xw::smem_bytes(BN), stream>>>(p);
+  xw::xw_kernel<BN, MODE, BRAW>
+      <<<dim3((unsigned)tiles, (unsigned)splits), xw::THREADS, xw::smem_bytes(BN, BRAW), stream>>>(p);
   GCNB_CHECK_CUDA(cudaGetLastError());
   return GCNB_OK;
 }
 
 template <int MODE>
-int launch_bn(int bn, const xw::Params& p, int64_t tiles, int splits, cudaStream_t stream) {
+int launch_bn(int bn, bool braw, const xw::Params& p, int64_t tiles, int splits, cudaStream_t stream) {
+  if (braw) {   // tall-K variant: bn <= 128
+    switch (bn) {
+      case 16: return launch_main<16, MODE, true>(p, tiles, splits, stream);
+      case 32: return launch_main<32, MODE, true>(p, tiles, splits, stream);
+      case 64: return launch_main<64, MODE, true>(p, tiles, splits, stream);
+      default: return launch_main<128, MODE, true>(p, tiles, splits, stream);
+    }
+  }
   switch (bn) {
-    case 16: return launch_main<16, MODE>(p, tiles, splits, stream);
-    case 32: return launch_main<32, MODE>(p, tiles, splits, stream);
-    case 64: return launch_main<64, MODE>(p, tiles, splits, stream);
-    case 256: return launch_main<256, MODE>(p, tiles, splits, stream);
-    default: return launch_main<128, MODE>(p, tiles, splits, stream);
+    case 16: return launch_main<16, MODE, false>(p, tiles, splits, stream);
+    case 32: return launch_main<32, MODE, false>(p, tiles, splits, stream);
+    case 64: return launch_main<64, MODE, false>(p, tiles, splits, stream);
+    case 256: return launch_main<256, MODE, false>(p, tiles, splits, stream);
+    default: return launch_main<128, MODE, false>(p, tiles, splits, stream);
   }
 }
 
@@ -451,7 +528,8 @@ extern "C" int gcnb_xw(const float* X, int64_t ldx, int trans_x, const float* W,
 
   if (K == 0) {   // empty sum: D = epilogue(0)
     const int64_t total = M * N;
-    xw::xw_reduce_kernel<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(nullptr, 0, M, N, D, ldd, bias, epilogue);
+    xw::xw_reduce_kernel<<<(unsigned)((total + xw::kReduceElems - 1) / xw::kReduceElems), xw::kReduceElems * xw::kReduceLanes, 0, stream>>>(
+        nullptr, 0, M, N, D, ldd, bias, epilogue);
     GCNB_CHECK_CUDA(cudaGetLastError());
     return GCNB_OK;
   }
@@ -460,15 +538,35 @@ extern "C" int gcnb_xw(const float* X, int64_t ldx, int trans_x, const float* W,
   // shared memory leave one 4-warp CTA per SM: measured slower (products epoch 23.3 vs 21.9 ms,
   // profiles/r01_ae_*), so it stays an experiment switch
   static const int wide = getenv("GCNB_XW_BN256") ? atoi(getenv("GCNB_XW_BN256")) : 0;
-  const int bn = N <= 16 ? 16 : (N <= 32 ? 32 : (N <= 64 ? 64 : ((N > 128 && wide) ? 256 : 128)));
+  const int64_t mtiles = (M + xw::BM - 1) / xw::BM;
+  // tall K, both operands vertex-sized (dW = X^T·dS): convert the second operand in the kernel instead
+  // of writing and re-reading an image of it.  Read per call so that a test can compare the two paths.
+  const char* tallk_env = getenv("GCNB_XW_TALLK");
+  const bool braw = (tallk_env ? atoi(tallk_env) != 0 : true) && !trans_w && mtiles <= 4 && K >= 4096;
+  const char* tallk_bn_env = getenv("GCNB_XW_TALLK_BN");   // experiment: 64 = two CTAs per SM, X converted per n-tile
+  const int wide_bn = braw ? ((tallk_bn_env && atoi(tallk_bn_env) == 64) ? 64 : 128) : ((N > 128 && wide) ? 256 : 128);
+  const int bn = N <= 16 ? 16 : (N <= 32 ? 32 : (N <= 64 ? 64 : wide_bn));
   const int ntiles = (N + bn - 1) / bn;
   const int nkb = (K + xw::BK - 1) / xw::BK;
-  const int64_t mtiles = (M + xw::BM - 1) / xw::BM;
   const int64_t tiles = mtiles * ntiles;
   GCNB_REQUIRE(tiles < 0x7fffffffLL, "too many tiles");
   const int n_sm = sm_count(dev);
+  // CTAs the split-K grid aims for: two per SM, or what the tall-K variant's shared memory leaves room for
+  const int ctas_per_sm = braw ? std::max(1, std::min(2, (227 * 1024) / (xw::smem_bytes(bn, true) + 1024))) : 2;
+  const int64_t want = (int64_t)ctas_per_sm * n_sm;
   int splits = 1;
-  if (tiles < 2 * n_sm && nkb > 1) splits = (int)std::min<int64_t>(nkb, (2 * n_sm + tiles - 1) / tiles);
+  if (tiles < want && nkb > 1) splits = (int)std::min<int64_t>(nkb, (want + tiles - 1) / tiles);
+  if (braw) {
+    // The TMEM accumulator does not round to nearest: the error of one split grows with the number of
+    // MMAs chained into it (measured: K = 33 333 in 25 splits, 1.05e-5 of max|D|; K = 2.4 M in 74 vs 148
+    // splits differ by 1.3e-4).  Bound the chain; the partial sums are added in fp32 round-to-nearest.
+    // The partials stay under 1 GB.
+    const char* chain_env = getenv("GCNB_XW_MAX_CHAIN");
+    const int64_t max_chain = std::max(1, chain_env ? atoi(chain_env) : 64);   // k-blocks of 16 per split
+    const int64_t max_splits = std::max<int64_t>(1, std::min<int64_t>(65535, ((int64_t)1 << 28) / std::max<int64_t>(1, M * N)));
+    const int64_t by_chain = std::min<int64_t>(max_splits, (nkb + max_chain - 1) / max_chain);
+    splits = (int)std::max<int64_t>(splits, by_chain);
+  }
   const int kb_per_split = (nkb + splits - 1) / splits;
   splits = (nkb + kb_per_split - 1) / kb_per_split;
   GCNB_REQUIRE(splits <= 65535, "too many k splits");
@@ -476,9 +574,9 @@ extern "C" int gcnb_xw(const float* X, int64_t ldx, int trans_x, const float* W,
   uint8_t* img = nullptr;
   float* partial = nullptr;
   const size_t img_bytes = (size_t)ntiles * nkb * 2 * xw::b_part_bytes(bn);
-  GCNB_CHECK_CUDA(cudaMallocAsync(&img, img_bytes, stream));
-  if (precision != 0) GCNB_CHECK_CUDA(cudaMemsetAsync(img, 0, img_bytes, stream));  // unused lo parts stay defined
-  {
+  if (!braw) {
+    GCNB_CHECK_CUDA(cudaMallocAsync(&img, img_bytes, stream));
+    if (precision != 0) GCNB_CHECK_CUDA(cudaMemsetAsync(img, 0, img_bytes, stream));  // unused lo parts stay defined
     const int64_t total = (int64_t)ntiles * bn * nkb * xw::BK;
     const unsigned blocks = (unsigned)((total + 255) / 256);
     if (precision == 0) xw::prep_w_kernel<0><<<blocks, 256, 0, stream>>>(W, ldw, trans_w, N, K, bn, nkb, ntiles, img);
@@ -488,6 +586,7 @@ extern "C" int gcnb_xw(const float* X, int64_t ldx, int trans_x, const float* W,
   }
   xw::Params p;
   p.X = X; p.ldx = ldx; p.trans_x = trans_x ? 1 : 0; p.w_img = img;
+  p.W = W; p.ldw = ldw; p.w_vec = aligned16(W) && (ldw % 4 == 0);
   p.M = M; p.N = N; p.K = K; p.nkb = nkb; p.ntiles = ntiles; p.kb_per_split = kb_per_split;
   p.x_vec = aligned16(X) && (ldx % 4 == 0);
   if (splits > 1) {
@@ -498,15 +597,16 @@ extern "C" int gcnb_xw(const float* X, int64_t ldx, int trans_x, const float* W,
     p.D = D; p.ldd = ldd; p.bias = bias; p.epi = epilogue;
     p.d_vec = aligned16(D) && (ldd % 4 == 0);
   }
-  if (precision == 0) rc = launch_bn<0>(bn, p, tiles, splits, stream);
-  else if (precision == 1) rc = launch_bn<1>(bn, p, tiles, splits, stream);
-  else rc = launch_bn<2>(bn, p, tiles, splits, stream);
+  if (precision == 0) rc = launch_bn<0>(bn, braw, p, tiles, splits, stream);
+  else if (precision == 1) rc = launch_bn<1>(bn, braw, p, tiles, splits, stream);
+  else rc = launch_bn<2>(bn, braw, p, tiles, splits, stream);
   if (rc == GCNB_OK && splits > 1) {
     const int64_t total = M * N;
-    xw::xw_reduce_kernel<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(partial, splits, M, N, D, ldd, bias, epilogue);
+    xw::xw_reduce_kernel<<<(unsigned)((total + xw::kReduceElems - 1) / xw::kReduceElems), xw::kReduceElems * xw::kReduceLanes, 0, stream>>>(
+        partial, splits, M, N, D, ldd, bias, epilogue);
     if (cudaGetLastError() != cudaSuccess) rc = set_error(GCNB_ERR_CUDA, "xw_reduce_kernel launch failed");
   }
-  cudaFreeAsync(img, stream);
+  if (img) cudaFreeAsync(img, stream);
   if (partial) cudaFreeAsync(partial, stream);
   return rc;
 }

@@ -66,6 +66,36 @@ def test_xw_tall_k_split_and_autograd():
     assert rel(Xs.grad, Xr.grad) < 1e-5 and rel(W.grad, Wr.grad) < 1e-5 and rel(b.grad, br.grad) < 1e-5
 
 
+@pytest.mark.parametrize("K,M,N", [(20_000, 256, 100), (20_000, 100, 256), (9_000, 256, 47), (5_000, 47, 256),
+                                   (4_100, 16, 7), (33_333, 300, 130), (4_096, 128, 128)])
+@pytest.mark.parametrize("precision", [0, 1, 2])
+def test_xw_tall_k_raw_second_operand(K, M, N, precision, monkeypatch):
+    """Tall-K variant (GCNB_XW_TALLK=1): the second operand of dW = Xᵀ·dS is converted inside the kernel
+    instead of through the prepared image.  Same numbers as the image path, both against fp64.
+    The TMEM accumulator does not round to nearest, so the error grows with the MMAs chained into one
+    split (xw_tcgen05.cu bounds the chain); the longest K gets twice the fp32 tolerance."""
+    tol = TOL[precision] * (2 if K > 30_000 else 1)
+    g = torch.Generator(device=DEV).manual_seed(K + M + N)
+    A = torch.randn(K, M, device=DEV, generator=g)
+    wide = torch.randn(K, N + 1, device=DEV, generator=g)
+    ref_of = lambda B: A.double().t() @ B.double()
+    for B in (wide[:, :N].contiguous(),      # leading dimension N (scalar copies when N % 4 != 0)
+              wide[:, :N],                   # a view: leading dimension N + 1
+              wide[:, 1:]):                  # a view whose base is 4-byte aligned only
+        ref = ref_of(B)
+        monkeypatch.setenv("GCNB_XW_TALLK", "1")
+        got = gemm.gemm_raw(A, B, trans_a=True, precision=precision)
+        monkeypatch.setenv("GCNB_XW_TALLK", "0")
+        img = gemm.gemm_raw(A, B, trans_a=True, precision=precision)
+        assert rel(got, ref) < tol, (K, M, N, precision, tuple(B.stride()))
+        assert rel(img, ref) < tol
+        assert rel(got, img.double()) < 2 * tol
+    # K-contiguous first operand (no transpose), tall K all the same
+    At = A.t().contiguous()
+    monkeypatch.setenv("GCNB_XW_TALLK", "1")
+    assert rel(gemm.gemm_raw(At, wide[:, :N].contiguous(), precision=precision), ref_of(wide[:, :N])) < tol
+
+
 def test_xw_degenerate():
     X = torch.randn(10, 0, device=DEV)
     W = torch.randn(0, 4, device=DEV)
