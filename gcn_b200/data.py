@@ -113,6 +113,28 @@ def largest_connected_component(adj) -> list:
     return [i for i, c in enumerate(comp) if c == keep]
 
 
+def get_train_val_test(nnodes: int, val_size=0.1, test_size=0.8, stratify=None, seed=None):
+    """The nettack / mettack split of the reference's small graphs — 10 % training, 10 % validation, 80 %
+    test, stratified by label (pygcn/gcnio/util/utils.py:270-297, called from dataio.py:36-39 with
+    seed 15).  Two sklearn ``train_test_split`` calls drawing from numpy's global generator after
+    ``np.random.seed(seed)``, as there, so the same seed gives the same three index arrays."""
+    from sklearn.model_selection import train_test_split
+
+    if stratify is None:
+        raise ValueError("stratify cannot be None")
+    if seed is not None:
+        np.random.seed(seed)
+    idx = np.arange(nnodes)
+    train_size = 1 - val_size - test_size
+    idx_train_and_val, idx_test = train_test_split(idx, random_state=None, train_size=train_size + val_size,
+                                                   test_size=test_size, stratify=stratify)
+    stratify = np.asarray(stratify)[idx_train_and_val]
+    idx_train, idx_val = train_test_split(idx_train_and_val, random_state=None,
+                                          train_size=train_size / (train_size + val_size),
+                                          test_size=val_size / (train_size + val_size), stratify=stratify)
+    return idx_train, idx_val, idx_test
+
+
 def split_indices(role: dict):
     """(idx_train, idx_val, idx_test) int64 arrays from a GraphSAINT role map (profiling_gcn.py:131-133)."""
     return (np.asarray(role["tr"], dtype=np.int64), np.asarray(role["va"], dtype=np.int64),

@@ -94,6 +94,11 @@ def main():
                     f = features.tocsr(); f.sort_indices()
                     out[k + "_f_indptr"], out[k + "_f_indices"], out[k + "_f_data"] = f.indptr, f.indices, f.data
                     out[k + "_labels"] = np.asarray(labels)
+    # nettack split of the small graphs (utils.py:270-297), seed 15 as profiling_gcn.py / dataio.py use
+    from pygcn.gcnio.util.utils import get_train_val_test
+    lab = np.random.default_rng(4).integers(0, 4, 200)
+    out["split_labels"] = lab
+    out["split_train"], out["split_val"], out["split_test"] = get_train_val_test(200, stratify=lab, seed=15)
     np.savez_compressed(os.path.join(HERE, "loaders.npz"), **out)
     print({k: v.shape for k, v in out.items()})
 

@@ -68,3 +68,16 @@ def test_loaded_graph_feeds_the_host_pipeline(tmp_path):
     rp, ci, va, vomp = graph.renumber_rabbit(A.indptr, A.indices, A.data)
     assert sorted(vomp.tolist()) == list(range(A.shape[0])) and rp[-1] == A.nnz
     assert feats[vomp].shape == feats.shape and labels[vomp].shape == labels.shape
+
+
+def test_nettack_split_matches_reference(golden):
+    """10 % / 10 % / 80 % stratified split of the small graphs (utils.py:270-297) with the reference's
+    seed: same three index arrays as the reference's function returned for the same labels."""
+    lab = golden["split_labels"]
+    tr, va, te = data.get_train_val_test(len(lab), stratify=lab, seed=15)
+    assert np.array_equal(tr, golden["split_train"])
+    assert np.array_equal(va, golden["split_val"])
+    assert np.array_equal(te, golden["split_test"])
+    assert len(np.unique(np.concatenate([tr, va, te]))) == len(lab)
+    with pytest.raises(ValueError):
+        data.get_train_val_test(10, stratify=None)
