@@ -57,6 +57,9 @@ def parse():
                     help="spmm: one C = A·B pass (headline); epoch: one 2-layer GCN training epoch")
     ap.add_argument("--order", default="none", choices=["none", "deg", "rcm", "gorder", "rabbit"],
                     help="host vertex reordering applied to the graph before the plan is built")
+    ap.add_argument("--wire", default="f32", choices=["f32", "bf16"],
+                    help="multi-GPU: dtype of the rows the ranks exchange (bf16 halves the NVLink bytes; the "
+                         "result is then within the bf16 tolerance, 1e-2)")
     ap.add_argument("--exchange", default="pull", choices=["pull", "allgather"],
                     help="N>1: how remote feature rows arrive — our P2P halo pull over NVLink peer memory, "
                          "or an NCCL all-gather of the whole operand")
@@ -490,7 +493,8 @@ def run_epoch_multi(args):
     name, rp, ci, va, n, _ = make_workload(args, device)
     nnz = int(rp[-1])
     nfeat, nhid, nclass = EPOCH_SHAPES[args.workload]
-    part = gdist.PartitionedSpMM(rp, ci, va, n, device=device, symmetric=True, exchange=args.exchange)
+    part = gdist.PartitionedSpMM(rp, ci, va, n, device=device, symmetric=True, exchange=args.exchange,
+                                 wire_dtype=torch.bfloat16 if args.wire == "bf16" else None)
     g = torch.Generator(device=device).manual_seed(15 + rank)
     X = torch.randn(part.m_local, nfeat, device=device, generator=g)
     labels = torch.randint(0, nclass, (part.m_local,), device=device, generator=g)
@@ -526,12 +530,15 @@ def run_multi(args):
     dist.init_process_group("nccl", device_id=device)
     name, rp, ci, va, n, k = make_workload(args, device)   # same seed on every rank -> same graph
     nnz = int(rp[-1])
-    part = gdist.PartitionedSpMM(rp, ci, va, n, device=device, symmetric=True, exchange=args.exchange)
+    wire = torch.bfloat16 if args.wire == "bf16" else None
+    in_slot = args.exchange == "pull" and wire is None   # fp32 operands are produced inside the exchange slot
+    part = gdist.PartitionedSpMM(rp, ci, va, n, device=device, symmetric=True, exchange=args.exchange,
+                                 wire_dtype=wire)
     local_nnz = int(part.fwd["local_csr"][0][-1])
     remote_nnz = int(part.fwd["remote_csr"][0][-1])
     g = torch.Generator(device=device).manual_seed(15 + rank)
     B = torch.randn(part.m_local, k, device=device, generator=g)
-    if args.exchange == "pull":
+    if in_slot:
         # the operand is resident where its producer would have written it: the exchange slot
         # (gcn_b200.dist.PartitionedGCN does that with the X·W product)
         slot = part.next_operand(k)
@@ -562,7 +569,7 @@ def run_multi(args):
     if not args.no_e2e:
         Bh = torch.randn(part.m_local, k, generator=torch.Generator().manual_seed(15 + rank)).pin_memory()
         Ch = torch.empty(part.m_local, k).pin_memory()
-        dst_ag = None if args.exchange == "pull" else torch.empty(part.m_local, k, device=device)
+        dst_ag = None if in_slot else torch.empty(part.m_local, k, device=device)
 
         def e2e_step():
             # pull mode: the upload lands in the free exchange slot, alternating like any producer does
@@ -598,16 +605,18 @@ def run_multi(args):
         abytes, flops = synth.spmm_bytes_flops(n, n, nnz, k)
         peak, peak_src = peaks()
         achieved = abytes / (ms_avg * 1e-3) / 1e9
-        gathered = int(halo_rows) * k * 4
+        gathered = int(halo_rows) * k * (2 if args.wire == "bf16" else 4)
         print(json.dumps({
             "metric": METRIC, "value": flops / (ms_avg * 1e-3) / 1e9, "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_avg, "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32" if args.wire == "f32" else "f32 (remote rows rounded to bf16 on the wire)",
+            "data": "synthetic",
             "config": {"workload": f"{name} SpMM C=A·B, k={k}, 1-D row partition by nnz over {world} GPUs, "
                                    + ("halo rows pulled over NVLink peer memory (gcnb_pull_rows)"
                                       if args.exchange == "pull" else "NCCL all-gather of B")
                                    + " overlapped with the local-column block",
-                       "n": n, "nnz": nnz, "k": k, "exchange": args.exchange,
+                       "n": n, "nnz": nnz, "k": k, "exchange": args.exchange, "wire": args.wire,
                        "local_nnz_frac": stats[0].item() / max(nnz, 1),
                        "exchange_bytes_received_per_rank_max": gathered,
                        "l2": "operands >> L2; no flush needed"},

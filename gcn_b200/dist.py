@@ -108,13 +108,15 @@ class _PeerExchange:
 
     Collective to construct (handles travel by ``all_gather_object``)."""
 
-    def __init__(self, rows: int, k: int, device, group):
+    def __init__(self, rows: int, k: int, device, group, dtype=torch.float32):
         import ctypes
         from . import _ffi
         self._ffi, self._ct = _ffi, ctypes
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
         self.device, self.rows, self.k = device, int(rows), int(k)
-        self.slot_bytes = ((self.rows * self.k * 4 + 255) // 256) * 256
+        self.dtype = dtype
+        self.esize = torch.empty(0, dtype=dtype).element_size()
+        self.slot_bytes = ((self.rows * self.k * self.esize + 255) // 256) * 256
         ptr = ctypes.c_void_p()
         handle = (ctypes.c_ubyte * 64)()
         _ffi.call("gcnb_peer_alloc", device.index, 2 * self.slot_bytes, ctypes.byref(ptr), handle)
@@ -138,9 +140,13 @@ class _PeerExchange:
         class _Raw:   # CUDA array interface view of the raw allocation (the library owns the memory)
             pass
         raw = _Raw()
-        raw.__cuda_array_interface__ = {"shape": (self.rows, self.k), "typestr": "<f4", "data": (ptr, False),
+        # bfloat16 has no type string in the array interface: map the bytes as int16 and reinterpret
+        typestr = {4: "<f4", 2: "<i2"}[self.esize]
+        raw.__cuda_array_interface__ = {"shape": (self.rows, self.k), "typestr": typestr, "data": (ptr, False),
                                         "version": 2, "strides": None}
         t = torch.as_tensor(raw, device=self.device)
+        if t.dtype != self.dtype:
+            t = t.view(self.dtype)
         assert t.data_ptr() == ptr
         return t
 
@@ -161,10 +167,17 @@ class PartitionedSpMM:
     """Row block `rank` of Â (and of Âᵀ unless symmetric) prepared for the gathered SpMM."""
 
     def __init__(self, rowptr, col, val, n: int, group=None, device=None, bounds=None,
-                 symmetric: bool | None = None, exchange: str = "allgather"):
+                 symmetric: bool | None = None, exchange: str = "allgather", wire_dtype=None):
         if exchange not in ("allgather", "pull"):
             raise ValueError("exchange must be 'allgather' or 'pull'")
+        if wire_dtype not in (None, torch.float32, torch.bfloat16):
+            raise ValueError("wire_dtype must be None / torch.float32 / torch.bfloat16")
         self.exchange = exchange
+        # "bf16 on the wire" (SURVEY.md §8e): the rows a rank publishes for its peers are rounded to
+        # bfloat16, which halves the NVLink bytes and the gather bytes of the remote-column block; the
+        # local-column block still multiplies the rank's own fp32 rows.  The result is then within the
+        # bf16-feature tolerance of the north star (1e-2), not the fp32 one, so it is opt-in.
+        self.wire_dtype = torch.float32 if wire_dtype is None else wire_dtype
         self._exchanges = {}     # k -> _PeerExchange
         self._halo_bufs = {}     # (id(blocks), k) -> compact halo rows
         self._flag = None
@@ -226,11 +239,11 @@ class PartitionedSpMM:
 
     def _gathered(self, blocks, B_local):
         k = B_local.shape[1]
-        padded = B_local
+        padded = B_local.to(self.wire_dtype)
         if self.m_local != self.stride:
-            padded = B_local.new_zeros((self.stride, k))
+            padded = padded.new_zeros((self.stride, k))
             padded[: self.m_local] = B_local
-        full = B_local.new_empty((self.world * self.stride, k))
+        full = padded.new_empty((self.world * self.stride, k))
         dist.all_gather_into_tensor(full, padded.contiguous(), group=self.group)
         return full
 
@@ -238,15 +251,15 @@ class PartitionedSpMM:
     def _exchange_for(self, k: int):
         ex = self._exchanges.get(k)
         if ex is None:   # collective: every rank reaches its first SpMM of width k together
-            ex = self._exchanges[k] = _PeerExchange(self.stride, k, self.device, self.group)
+            ex = self._exchanges[k] = _PeerExchange(self.stride, k, self.device, self.group, self.wire_dtype)
         return ex
 
     def next_operand(self, k: int):
         """Pull mode: a [m_local × k] float32 view of the free exchange slot for the producer of the
         next operand (``gemm.xw(..., out=part.next_operand(k))``): an operand that already lives there
         is published without a copy.  Collective on first use of a width.  None in all-gather mode."""
-        if self.exchange != "pull":
-            return None
+        if self.exchange != "pull" or self.wire_dtype != torch.float32:
+            return None     # a bf16 slot cannot hold the producer's fp32 result: it is cast on publish
         ex = self._exchange_for(k)
         slot = ex.turn
         ex.turn ^= 1
@@ -256,11 +269,12 @@ class PartitionedSpMM:
         """Make the local block visible to the peers; returns the slot it is in.  A block that was
         produced in place (next_operand) is already there; anything else is copied into the free slot."""
         for slot in (0, 1):
-            if B_local.data_ptr() == ex.own[slot].data_ptr() and B_local.stride(0) == ex.k:
+            if (B_local.dtype == ex.dtype and B_local.data_ptr() == ex.own[slot].data_ptr()
+                    and B_local.stride(0) == ex.k):
                 return slot
         slot = ex.turn
         ex.turn ^= 1
-        ex.own[slot][: self.m_local].copy_(B_local)
+        ex.own[slot][: self.m_local].copy_(B_local)     # rounds to the wire dtype when they differ
         return slot
 
     def _rank_barrier(self):
@@ -277,13 +291,14 @@ class PartitionedSpMM:
         key = (id(blocks), k)
         halo = self._halo_bufs.get(key)
         if halo is None:
-            halo = self._halo_bufs[key] = torch.empty((blocks["n_remote_cols"], k), dtype=torch.float32,
+            halo = self._halo_bufs[key] = torch.empty((blocks["n_remote_cols"], k), dtype=self.wire_dtype,
                                                       device=self.device)
         if n_halo:
-            _ffi.call("gcnb_pull_rows", ex.bases(slot), self.world, k * 4,
+            row_bytes = k * halo.element_size()
+            _ffi.call("gcnb_pull_rows", ex.bases(slot), self.world, row_bytes,
                       ctypes.c_void_p(blocks["halo_part"].data_ptr()),
                       ctypes.c_void_p(blocks["halo_row"].data_ptr()), ctypes.c_void_p(halo.data_ptr()),
-                      k * 4, n_halo, k * 4, blocks["halo_first"],
+                      row_bytes, n_halo, row_bytes, blocks["halo_first"],
                       ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream))
         return halo
 

@@ -68,7 +68,7 @@ class _OraclePart(gdist.PartitionedSpMM):
 
     def _mul_remote_accumulate(self, blocks, B_gathered, out):
         rp, ci, va = blocks["remote_csr"]
-        out.add_(torch.from_numpy(SO.spmm_f32(rp, ci, va, B_gathered.shape[0], B_gathered.numpy())))
+        out.add_(torch.from_numpy(SO.spmm_f32(rp, ci, va, B_gathered.shape[0], B_gathered.float().numpy())))
 
 
 class _OraclePartPull(_OraclePart):
@@ -79,7 +79,7 @@ class _OraclePartPull(_OraclePart):
         return None
 
     def _publish(self, ex, B_local):
-        self._published = B_local
+        self._published = B_local.to(self.wire_dtype).float()   # what the peers would read
         return 0
 
     def _pull(self, blocks, ex, slot, k):
@@ -169,3 +169,51 @@ def test_two_rank_gathered_spmm_gloo(symmetric, exchange):
     assert spans[0][0] == 0 and spans[0][1] == spans[1][0] and spans[1][1] == 257
     for rank, fwd, bwd, ok, _ in res:
         assert fwd < 1e-5 and bwd < 1e-5 and ok, (rank, fwd, bwd, ok)
+
+
+def _wire_worker(rank, world, port, exchange, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        A = random_normalized_graph(257, 1800, 9, "skew")
+        n = A.shape[0]
+        B = np.random.default_rng(1).standard_normal((n, 6)).astype(np.float32)
+        cls = _OraclePartPull if exchange == "pull" else _OraclePart
+        part = cls(A.indptr, A.indices, A.data, n, device="cpu", exchange=exchange, wire_dtype=torch.bfloat16)
+        assert part.next_operand(6) is None              # no fp32 producer slot with a bf16 wire
+        lo, hi = part.lo, part.hi
+        out = part.forward(torch.from_numpy(B[lo:hi].copy())).numpy()
+        # expected: own rows in fp32, every other rank's rows rounded to bf16
+        Bw = torch.from_numpy(B).to(torch.bfloat16).float().numpy()
+        Bw[lo:hi] = B[lo:hi]
+        want = SO.spmm_f64(A.indptr, A.indices, A.data, n, Bw)[lo:hi]
+        exact = SO.spmm_f64(A.indptr, A.indices, A.data, n, B)[lo:hi]
+        q.put((rank, rel_err(out, want), rel_err(out, exact)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("exchange", ["allgather", "pull"])
+def test_bf16_on_the_wire_gloo(exchange):
+    """wire_dtype=bfloat16: remote rows arrive rounded to bf16, the rank's own rows stay fp32."""
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_wire_worker, args=(r, world, port, exchange, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, to_model, to_exact in res:
+        assert to_model < 1e-5, (rank, to_model)          # exactly the rounding described, nothing else
+        assert 1e-5 < to_exact < 1e-2, (rank, to_exact)   # north_star tolerance for bf16 features
+
+
+def test_wire_dtype_is_validated():
+    with pytest.raises(ValueError, match="wire_dtype"):
+        gdist.PartitionedSpMM.__init__(object.__new__(gdist.PartitionedSpMM), [0, 0], [], [], 1,
+                                       wire_dtype=torch.float16)
