@@ -556,7 +556,7 @@ extern "C" int gcnb_xw(const float* X, int64_t ldx, int trans_x, const float* W,
   const int64_t want = (int64_t)ctas_per_sm * n_sm;
   int splits = 1;
   if (tiles < want && nkb > 1) splits = (int)std::min<int64_t>(nkb, (want + tiles - 1) / tiles);
-  if (braw) {
+  if (braw || (K >= 4096 && mtiles <= 8)) {   // tall K, small output: partials are cheap
     // The TMEM accumulator does not round to nearest: the error of one split grows with the number of
     // MMAs chained into it (measured: K = 33 333 in 25 splits, 1.05e-5 of max|D|; K = 2.4 M in 74 vs 148
     // splits differ by 1.3e-4).  Bound the chain; the partial sums are added in fp32 round-to-nearest.
