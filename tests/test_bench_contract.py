@@ -66,3 +66,17 @@ def test_reference_epoch_arm_line():
     r = _run("--impl", "reference", "--mode", "epoch", "--workload", "rmat", "--scale", "18", "--edge-factor", "16")
     d = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][0])
     assert r.returncode == 0 and "unavailable" in d
+
+
+def test_defaults_and_multi_gpu_switches(monkeypatch):
+    """With no flags: N = 1 and a K/W that finish within minutes (W >= 3); the multi-GPU switches parse."""
+    sys.path.insert(0, ROOT)
+    import bench
+    monkeypatch.setattr(sys, "argv", ["bench.py"])
+    a = bench.parse()
+    assert a.gpus == 1 and a.warmup >= 3 and a.steps >= 1 and a.impl == "ours" and a.mode == "spmm"
+    assert a.workload == "products" and a.exchange == "pull" and a.wire == "f32"
+    monkeypatch.setattr(sys, "argv", ["bench.py", "--gpus", "8", "--exchange", "allgather", "--wire", "bf16",
+                                      "--mode", "epoch"])
+    a = bench.parse()
+    assert (a.gpus, a.exchange, a.wire, a.mode) == (8, "allgather", "bf16", "epoch")
