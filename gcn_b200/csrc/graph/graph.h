@@ -5,11 +5,47 @@
 // but on flat CSR arrays: no edge-list of pairs, no per-vertex std::vector, no std::map.
 #pragma once
 #include <stdint.h>
+#include <stdlib.h>
 
+#include <algorithm>
+#include <thread>
 #include <vector>
 
 namespace gcnb {
 namespace graph {
+
+// Host threads for the loops whose iterations are independent (one row each): the hardware's, at most
+// 16, or GCNB_HOST_THREADS.  The per-row work is unchanged, so the results are.
+inline int host_threads() {
+  const char* e = getenv("GCNB_HOST_THREADS");
+  int t = e ? atoi(e) : (int)std::min(16u, std::max(1u, std::thread::hardware_concurrency()));
+  return std::max(1, t);
+}
+
+// fn(begin, end) over [0, n) cut into contiguous chunks of about equal weight, where
+// prefix[i+1] - prefix[i] is the weight of item i (a CSR row pointer); one thread per chunk.
+template <typename Prefix, typename Fn>
+void parallel_rows(int64_t n, const Prefix& prefix, Fn fn) {
+  const int64_t total = (int64_t)prefix[n] - (int64_t)prefix[0];
+  const int t = (int)std::min<int64_t>(host_threads(), std::max<int64_t>(1, total / (1 << 16)));
+  if (t <= 1 || n < 2) {
+    fn((int64_t)0, n);
+    return;
+  }
+  std::vector<int64_t> cut((size_t)t + 1, n);
+  cut[0] = 0;
+  int64_t i = 0;
+  for (int c = 1; c < t; ++c) {
+    const int64_t want = (int64_t)prefix[0] + total * c / t;
+    while (i < n && (int64_t)prefix[i] < want) ++i;
+    cut[(size_t)c] = i;
+  }
+  std::vector<std::thread> pool;
+  for (int c = 1; c < t; ++c)
+    if (cut[(size_t)c] < cut[(size_t)c + 1]) pool.emplace_back(fn, cut[(size_t)c], cut[(size_t)c + 1]);
+  fn(cut[0], cut[1]);
+  for (auto& th : pool) th.join();
+}
 
 struct CsrView {
   const int32_t* rowptr;

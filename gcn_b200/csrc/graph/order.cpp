@@ -50,8 +50,9 @@ FlatAdj relabelled_lists(const CsrView& g, const std::vector<int64_t>& rank, boo
       else a.adj[(size_t)cur[ru]++] = (uint32_t)rv;
     }
   }
-  for (int64_t u = 0; u < n; ++u)
-    std::sort(a.adj.begin() + a.off[u], a.adj.begin() + a.off[u + 1]);
+  parallel_rows(n, a.off, [&](int64_t u0, int64_t u1) {
+    for (int64_t u = u0; u < u1; ++u) std::sort(a.adj.begin() + a.off[u], a.adj.begin() + a.off[u + 1]);
+  });
   return a;
 }
 

@@ -23,24 +23,27 @@ void perm_apply(int32_t* rowptr, int32_t* col, float* val, const int32_t* vomp, 
   }
   std::vector<int32_t> new_col((size_t)nnz);
   std::vector<float> new_val((size_t)nnz);
-  std::vector<std::pair<int32_t, float>> row;
-  for (int64_t i = 0; i < m; ++i) {
-    const int32_t old = vomp[i];
-    const int64_t b = rowptr[old], e = rowptr[old + 1];
-    row.clear();
-    for (int64_t z = b; z < e; ++z) row.emplace_back(to_new[(size_t)col[z]], val[z]);
-    // column ids within a row are distinct, so the order is fully determined
-    std::sort(row.begin(), row.end(),
-              [](const std::pair<int32_t, float>& x, const std::pair<int32_t, float>& y) {
-                return x.first < y.first;
-              });
-    int64_t p = new_rowptr[i];
-    for (const auto& cv : row) {
-      new_col[(size_t)p] = cv.first;
-      new_val[(size_t)p] = cv.second;
-      ++p;
+  // rows are independent: one contiguous range of new rows per host thread, balanced by non-zeros
+  parallel_rows(m, new_rowptr, [&](int64_t r0, int64_t r1) {
+    std::vector<std::pair<int32_t, float>> row;
+    for (int64_t i = r0; i < r1; ++i) {
+      const int32_t old = vomp[i];
+      const int64_t b = rowptr[old], e = rowptr[old + 1];
+      row.clear();
+      for (int64_t z = b; z < e; ++z) row.emplace_back(to_new[(size_t)col[z]], val[z]);
+      // column ids within a row are distinct, so the order is fully determined
+      std::sort(row.begin(), row.end(),
+                [](const std::pair<int32_t, float>& x, const std::pair<int32_t, float>& y) {
+                  return x.first < y.first;
+                });
+      int64_t p = new_rowptr[i];
+      for (const auto& cv : row) {
+        new_col[(size_t)p] = cv.first;
+        new_val[(size_t)p] = cv.second;
+        ++p;
+      }
     }
-  }
+  });
   std::copy(new_rowptr.begin(), new_rowptr.end(), rowptr);
   std::copy(new_col.begin(), new_col.end(), col);
   std::copy(new_val.begin(), new_val.end(), val);

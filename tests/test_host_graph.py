@@ -163,3 +163,35 @@ def test_compat_shim_host_entry_points(golden_graph):
         _ffi.lib.csr2seg_Cmajor(ridx, p(rp), p(ci), p(va), m, m, nnz, p(ident), p(svm), p(srp), p(scv), 8, p(cnt))
     assert cnt[0] == ns and np.array_equal(svm, g["tile_segVoMap"])
     assert np.array_equal(srp, g["tile_seg_rowPtr"]) and np.array_equal(scv, g["tile_segNzCV"])
+
+
+def test_threaded_row_loops_change_nothing(monkeypatch):
+    """perm_apply and the relabelled adjacency lists sort their rows on several host threads once the
+    graph is large enough (graph.h: parallel_rows); the result must be the single-threaded one, and
+    (where oracle/_ref is built) the reference's."""
+    A = random_normalized_graph(4000, 300_000, 77, "skew")      # ~600k non-zeros: 8+ chunks of 64k
+    rp, ci, va = A.indptr, A.indices, A.data
+    assert rp[-1] > 8 * (1 << 16)
+    vomp = np.random.default_rng(5).permutation(A.shape[0]).astype(np.int32)
+    got = {}
+    for threads in ("1", "5", "16"):
+        monkeypatch.setenv("GCNB_HOST_THREADS", threads)
+        got[threads] = (graph.perm_apply(rp, ci, va, vomp), graph.order_rcm(rp, ci),
+                        graph.renumber_rcm(rp, ci, va), graph.order_gorder(rp, ci, 3))
+    for threads in ("5", "16"):
+        for a, b in zip(got["1"], got[threads]):
+            if isinstance(a, tuple):
+                assert all(np.array_equal(x, y) for x, y in zip(a, b))
+            else:
+                assert np.array_equal(a, b)
+    # the permuted matrix really is P·A·Pᵀ with sorted rows
+    import scipy.sparse as sp
+    prp, pci, pva = got["5"][0][:3]
+    P = sp.csr_matrix((pva, pci, prp), shape=A.shape)
+    want = A[vomp][:, vomp].tocsr()
+    want.sort_indices()
+    assert np.array_equal(P.indptr, want.indptr) and np.array_equal(P.indices, want.indices)
+    assert np.array_equal(P.data, want.data)
+    if R.have("ref_graph.so"):
+        monkeypatch.setenv("GCNB_HOST_THREADS", "7")
+        assert np.array_equal(graph.order_rcm(rp, ci), R.ref_order_rcm(rp, ci))
