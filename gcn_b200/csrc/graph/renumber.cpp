@@ -2,6 +2,7 @@
 // identical tails of gorder() :190-229 and dfs() :97-154) and the DFS pre-order
 // (renumber.cu:56-95).
 #include <algorithm>
+#include <memory>
 #include <utility>
 
 #include "graph.h"
@@ -21,8 +22,9 @@ void perm_apply(int32_t* rowptr, int32_t* col, float* val, const int32_t* vomp, 
     to_new[(size_t)old] = (int32_t)i;
     new_rowptr[i + 1] = new_rowptr[i] + (rowptr[old + 1] - rowptr[old]);
   }
-  std::vector<int32_t> new_col((size_t)nnz);
-  std::vector<float> new_val((size_t)nnz);
+  // uninitialised scratch (every element is written below): no 8·nnz-byte memset
+  std::unique_ptr<int32_t[]> new_col(new int32_t[(size_t)std::max<int64_t>(nnz, 1)]);
+  std::unique_ptr<float[]> new_val(new float[(size_t)std::max<int64_t>(nnz, 1)]);
   // rows are independent: one contiguous range of new rows per host thread, balanced by non-zeros
   parallel_rows(m, new_rowptr, [&](int64_t r0, int64_t r1) {
     std::vector<std::pair<int32_t, float>> row;
@@ -45,8 +47,11 @@ void perm_apply(int32_t* rowptr, int32_t* col, float* val, const int32_t* vomp, 
     }
   });
   std::copy(new_rowptr.begin(), new_rowptr.end(), rowptr);
-  std::copy(new_col.begin(), new_col.end(), col);
-  std::copy(new_val.begin(), new_val.end(), val);
+  parallel_rows(m, new_rowptr, [&](int64_t r0, int64_t r1) {
+    const int64_t b = new_rowptr[r0], e = new_rowptr[r1];
+    std::copy(new_col.get() + b, new_col.get() + e, col + b);
+    std::copy(new_val.get() + b, new_val.get() + e, val + b);
+  });
 }
 
 void dfs_order(const CsrView& g, int32_t* vomp) {
