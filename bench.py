@@ -11,9 +11,18 @@ configuration BASELINE.json's target ("≥60 % of HBM roofline on ogbn-products-
 GPU") is quoted on and the one its 1/2/4/8-GPU row-partitioned runs use.  B (≈0.98 GB) is far
 larger than L2, so every timed iteration streams from HBM; no explicit flush is needed.
 
-N > 1 (launched by torchrun, one rank per GPU): the same graph, row-partitioned by non-zeros,
-all-gather of B over NCCL overlapped with the local-column block (gcn_b200/dist.py) — strong
-scaling, value = total flops ÷ max-over-ranks device time.
+N > 1 (launched by torchrun, one rank per GPU): the same graph, row-partitioned by non-zeros; the
+remote rows of B arrive by our halo pull over NVLink peer memory (default, --exchange pull) or by an
+NCCL all-gather of B (--exchange allgather), overlapped with the local-column block
+(gcn_b200/dist.py) — strong scaling, value = total flops ÷ max-over-ranks device time.  Every N > 1
+line carries an untimed `parity_check`: consecutive steps with fresh operands under the real
+stream-ordered rank barrier, sampled rows against an fp64 host evaluation; the run exits non-zero
+above the tolerance.
+
+The default line also carries `epoch` (the second half of BASELINE.json's metric: one 2-layer GCN
+training epoch on the same graph) and, at N = 1, `gpu_comparators` (cuSPARSE CSR ALG3 as the
+reference's cuspmm.cu calls it, torch.spmm on CUDA as pygcn/gcn5.py:90 calls it, and with
+--comparators all the reference's own flexspmm kernel on its corrected tiles) on the same inputs.
 
 --impl reference: the reference's CPU implementation of the path — torch.spmm(adj, B) on COO
 tensors (pygcn/gcn1.py:53) — on the box's host cores, on a bounded row-slice sample.
@@ -73,7 +82,27 @@ def parse():
                     help="epoch mode, 1 GPU: replay the training step from a CUDA graph (model.GCN.graphed_step)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cpu-threads", type=int, default=0,
+                    help="host threads of the reference arm / cpu_baseline (default: every core this process may "
+                         "run on, also under torchrun, which exports OMP_NUM_THREADS=1)")
+    ap.add_argument("--comparators", default="fast", choices=["none", "fast", "all"],
+                    help="N=1 spmm mode: other GPU implementations timed on the same inputs (bench leg only): "
+                         "fast = cuSPARSE CSR ALG3 + torch.spmm CUDA; all = + the reference's flexspmm.so on its tiles")
+    ap.add_argument("--no-epoch", action="store_true", help="spmm mode: skip the `epoch` object of the line")
+    ap.add_argument("--no-parity", action="store_true", help="N>1: skip the untimed parity_check")
     return ap.parse_args()
+
+
+def host_threads(args):
+    """Thread count of the CPU legs: every core the process may run on, set explicitly so that the N = 1
+    and the torchrun (OMP_NUM_THREADS=1) arms time the reference on the same number of threads."""
+    try:
+        avail = len(os.sched_getaffinity(0))
+    except AttributeError:
+        avail = os.cpu_count() or 1
+    n = args.cpu_threads if getattr(args, "cpu_threads", 0) > 0 else avail
+    torch.set_num_threads(n)
+    return torch.get_num_threads()
 
 
 def kernel_launches_per_spmm(info, k, dtype):
@@ -212,10 +241,12 @@ def workload_string(name, k):
 
 
 # ---- CPU baseline: the reference's path on the host cores ------------------------------------------
-def cpu_reference_sample(rp, ci, va, n, k, budget_s=10.0, reps=1):
+def cpu_reference_sample(rp, ci, va, n, k, budget_s=10.0, reps=1, args=None):
     """torch.spmm(adj, B) on CPU (pygcn/gcn1.py:53) over a bounded row slice of the same Â.
     Returns (GFLOP/s, cores, sample description, seconds per call)."""
     from oracle import spmm_oracle as SO
+    if args is not None:
+        host_threads(args)
     nnz = int(rp[-1])
     # slice sized for roughly budget_s at a guessed 4 GFLOP/s; at least 1/64 of the rows
     want_nnz = min(nnz, max(nnz // 64, int(budget_s * 2e9 / (2 * k))))
@@ -239,6 +270,7 @@ def run_reference_epoch(args):
     """--impl reference --mode epoch: the reference's 2-layer GCN epoch on the host cores (torch CPU ops,
     pygcn/gcn1.py:62-118, :176-203, restated in oracle/spmm_oracle.py gcn_epoch_cpu), whole graph —
     only for the shapes where that takes seconds (Cora- and arxiv-shaped)."""
+    host_threads(args)
     name, rp, ci, va, n, _ = make_workload(args, "cuda" if torch.cuda.is_available() else "cpu")
     nnz = int(rp[-1])
     nfeat, nhid, nclass = EPOCH_SHAPES[args.workload]
@@ -283,6 +315,7 @@ def run_reference(args):
     if args.mode == "epoch":
         run_reference_epoch(args)
         return
+    host_threads(args)
     name, rp, ci, va, n, k = make_workload(args, "cuda" if torch.cuda.is_available() else "cpu")
     from oracle import spmm_oracle as SO
     nnz = int(rp[-1])
@@ -308,6 +341,137 @@ def run_reference(args):
                          "kind": "reference", "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
+
+
+# ---- GPU comparators (bench leg only; nothing here is on the product path) ----------------------------
+def _event_ms(fn, reps=5, warm=2):
+    """Device time of fn() by CUDA events on the current (= legacy default) stream.  A ~5 ms spin kernel is
+    queued first so that host-side stalls inside fn (the reference's per-call cudaGetDeviceProperties /
+    cusparseCreate) happen while the GPU is still busy and do not show up between the two events."""
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    out = []
+    for _ in range(reps):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda._sleep(10_000_000)
+        a.record()
+        fn()
+        b.record()
+        torch.cuda.synchronize()
+        out.append(a.elapsed_time(b))
+    out.sort()
+    return out[len(out) // 2]
+
+
+def gpu_comparators(args, rp, ci, va, n, k, B, C_ours, device, ours_ms):
+    """Other GPU implementations of C = Â·B on the SAME device-resident inputs:
+      cusparse_csr_alg3  cusparseSpMM(CSR, row-major dense, CUSPARSE_SPMM_CSR_ALG3) — the call of
+                         /root/reference/cuspmm.cu:57-61, per-call setup hoisted (oracle/cusparse_cmp.cu)
+      torch_spmm_cuda    torch.spmm(adj_coo, B) on CUDA — pygcn/gcn5.py:90, the reference's GPU layer
+      ref_flexspmm       (--comparators all) the reference's own flexspmm.so (unmodified flexspmm.cu built
+                         for sm_100a) on its corrected tile format, kernel time only
+    Each entry: median ms of 5, GFLOP/s, max relative deviation of its result from ours."""
+    import ctypes
+    res = {}
+    flops = 2.0 * int(rp[-1]) * k
+    if args.dtype != "f32" or B.stride(0) != k:
+        return {"skipped": "comparators run on contiguous fp32 operands only"}
+
+    def entry(ms, C, note):
+        err = float((C - C_ours).abs().max() / C_ours.abs().max())
+        return {"ms": ms, "gflops": flops / (ms * 1e-3) / 1e9, "ours_over_this": ms / ours_ms,
+                "max_rel_dev_from_ours": err, "note": note}
+
+    d_rp = torch.from_numpy(np.ascontiguousarray(rp, dtype=np.int32)).to(device)
+    d_ci = torch.from_numpy(np.ascontiguousarray(ci, dtype=np.int32)).to(device)
+    d_va = torch.from_numpy(np.ascontiguousarray(va, dtype=np.float32)).to(device)
+    Bc = B.contiguous()
+    C = torch.empty(n, k, device=device)
+    # -- cuSPARSE ALG3 (and ALG2, the one torch picks) with a persistent handle
+    lib_path = os.path.join(ROOT, "oracle", "libcusparse_cmp.so")
+    if os.path.exists(lib_path):
+        lib = ctypes.CDLL(lib_path)
+        lib.cmp_cusparse_create.argtypes = [ctypes.c_void_p] * 3 + [ctypes.c_longlong] * 3 + [ctypes.c_void_p] * 2 + \
+            [ctypes.c_int, ctypes.c_longlong, ctypes.c_longlong, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+        lib.cmp_cusparse_spmm.argtypes = [ctypes.c_void_p]
+        lib.cmp_cusparse_destroy.argtypes = [ctypes.c_void_p]
+        lib.cmp_cusparse_buffer_bytes.argtypes = [ctypes.c_void_p]
+        lib.cmp_cusparse_buffer_bytes.restype = ctypes.c_longlong
+        for alg, nm in ((0, "cusparse_csr_alg3"), (1, "cusparse_csr_alg2")):
+            h = ctypes.c_void_p()
+            rc = lib.cmp_cusparse_create(d_rp.data_ptr(), d_ci.data_ptr(), d_va.data_ptr(), n, n, int(rp[-1]),
+                                         Bc.data_ptr(), C.data_ptr(), k, k, k, alg,
+                                         torch.cuda.current_stream(device).cuda_stream, ctypes.byref(h))
+            if rc != 0:
+                res[nm] = {"error": f"cmp_cusparse_create rc={rc}"}
+                continue
+            ms = _event_ms(lambda: lib.cmp_cusparse_spmm(h))
+            res[nm] = entry(ms, C, f"cusparseSpMM CSR x row-major fp32, work buffer {lib.cmp_cusparse_buffer_bytes(h)} B, "
+                                   "handle/descriptors created once"
+                                   + ("; the algorithm /root/reference/cuspmm.cu:57-61 names" if alg == 0 else ""))
+            lib.cmp_cusparse_destroy(h)
+    else:
+        res["cusparse_csr_alg3"] = {"error": "oracle/libcusparse_cmp.so not built"}
+    # -- torch.spmm on CUDA, COO adjacency as the reference builds it (utils.py:243-250)
+    try:
+        row = torch.repeat_interleave(torch.arange(n, device=device), (d_rp[1:] - d_rp[:-1]).long())
+        adj = torch.sparse_coo_tensor(torch.stack((row, d_ci.long())), d_va, (n, n)).coalesce()
+        del row
+        holder = {}
+
+        def f():
+            holder["C"] = torch.spmm(adj, Bc)
+        ms = _event_ms(f)
+        res["torch_spmm_cuda"] = entry(ms, holder["C"], "torch.spmm(sparse COO fp32, dense) on CUDA, pygcn/gcn5.py:90")
+        del adj, holder
+    except Exception as e:   # noqa: BLE001 — a comparator that cannot run is reported, not fatal
+        res["torch_spmm_cuda"] = {"error": repr(e)[:200]}
+    # -- the reference's own kernel on its own (corrected) tiles
+    if args.comparators == "all":
+        from gcn_b200 import graph
+        from oracle import ref_bindings as R
+        if not R.have("flexspmm.so"):
+            res["ref_flexspmm"] = {"error": "oracle/_ref/flexspmm.so not shipped"}
+        elif n * k >= 2 ** 31 or n >= 2 ** 24:
+            res["ref_flexspmm"] = {"error": "reference limits: int32 row*k addressing (flexspmm.cu:67), float column ids (tile.cu:67)"}
+        else:
+            t0 = time.perf_counter()
+            n_sm = torch.cuda.get_device_properties(device).multi_processor_count
+            t = graph.csr2tile(rp, ci, va, n_sm=n_sm)     # bit-exact with the corrected reference builder (tests)
+            tile_s = time.perf_counter() - t0
+            lib = ctypes.CDLL(os.path.join(R.REF_DIR, "flexspmm.so"))
+            d = {key: torch.from_numpy(np.ascontiguousarray(t[key])).to(device)
+                 for key in ("seg_rowPtr", "segNzCV", "segVoMap", "grouped_tailSeg", "next_seg")}
+            Cf = torch.zeros(n, k, device=device)
+            nxt = d["next_seg"].clone()
+            vp = ctypes.c_void_p
+
+            def f():
+                Cf.zero_()                      # the reference allocates zeros and copies next_seg per call (gcn6.py:37-38)
+                nxt.copy_(d["next_seg"])
+
+            def g():
+                lib.flexspmm(vp(d["seg_rowPtr"].data_ptr()), vp(d["segNzCV"].data_ptr()), vp(d["segVoMap"].data_ptr()),
+                             vp(d["grouped_tailSeg"].data_ptr()), vp(nxt.data_ptr()), n, n, k, int(t["n_segs"]),
+                             vp(Bc.data_ptr()), vp(Cf.data_ptr()))
+            times = []
+            for i in range(5):
+                f()
+                torch.cuda.synchronize()
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                torch.cuda._sleep(10_000_000)
+                a.record()
+                g()
+                b.record()
+                torch.cuda.synchronize()
+                if i >= 2:
+                    times.append(a.elapsed_time(b))
+            times.sort()
+            res["ref_flexspmm"] = entry(times[len(times) // 2], Cf,
+                                        f"flexspmm.so (reference kernel, sm_100a build) on {int(t['n_segs'])} corrected tile-segments; "
+                                        f"kernel only (zeroing C and the next_seg copy outside the events); host tile build {tile_s:.1f} s")
+    return res
 
 
 # ---- our arm -------------------------------------------------------------------------------------
@@ -385,7 +549,9 @@ def run_single(args):
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": abytes,
-                     "note": "whole-step device time (stream kernel + split-row reduce, 99.84 % / 0.16 % of the device time in profiles/r01_ai_launches_products_k100.csv) used as the launch duration"},
+                     "note": f"whole-step device time of the {launches_per_step} launch(es) of one gcnb_spmm call (class kernel"
+                             + (" + fixed-order split-row reduce" if launches_per_step > 1 else "")
+                             + ") used as the launch duration; ncu launch lists under profiles/ give the shares"},
         "clocks": clk.summary(),
     }
     traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
@@ -395,8 +561,11 @@ def run_single(args):
                 tr = json.load(f)
             key = f"{args.workload}-k{k}-{args.dtype}"
             if key in tr:
+                # dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel from the committed
+                # `ncu --set full` capture named in traffic_source — NOT measured in this run
                 out["roofline"]["traffic"] = tr[key]["dram_bytes_per_launch"]
                 out["roofline"]["traffic_source"] = tr[key].get("source")
+                out["roofline"]["traffic_capture"] = tr[key].get("capture", "round 1")
         except Exception:
             pass
 
@@ -416,8 +585,22 @@ def run_single(args):
                       "d2h_bytes_per_step": n * k * 4, "ms_per_step": e2e_s * 1e3, "steps": reps,
                       "api": "gcnb_spmm_host (C ABI, pinned host buffers)"}
         del Bh, Ch
+    if args.comparators != "none":
+        plan.spmm(B, out=C)
+        try:
+            out["gpu_comparators"] = gpu_comparators(args, rp, ci, va, n, k, B, C, device, ms_med)
+        except Exception as e:   # noqa: BLE001
+            out["gpu_comparators"] = {"error": repr(e)[:300]}
+    del plan, B, C
+    torch.cuda.empty_cache()
+    if not args.no_epoch and args.workload in EPOCH_SHAPES:
+        try:
+            out["epoch"] = epoch_object_single(args, rp, ci, va, n, device)
+        except Exception as e:   # noqa: BLE001
+            out["epoch"] = {"error": repr(e)[:300]}
+        torch.cuda.empty_cache()
     if not args.no_cpu_baseline:
-        v, cores, sample, _ = cpu_reference_sample(rp, ci, va, n, k)
+        v, cores, sample, _ = cpu_reference_sample(rp, ci, va, n, k, args=args)
         out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample}
     print(json.dumps(out))
 
@@ -438,6 +621,67 @@ def epoch_line(args, name, n, nnz, world, ms_avg, ms_med, ms_min, clocks, extra)
            "ms_median": ms_med, "ms_min": ms_min, "clocks": clocks, "e2e": None}
     out.update(extra)
     return out
+
+
+def epoch_object_single(args, rp, ci, va, n, device):
+    """The second half of BASELINE.json's metric ("GCN epoch ms") on the SAME graph, for the default
+    line: one 2-layer GCN training epoch (forward, NLL on 5 % of the vertices, backward, Adam),
+    pygcn/gcn5.py:146-262 / gcn6.py:412-441, device-timed, plus end to end with the loss read back."""
+    from gcn_b200 import model as gmodel
+    from gcn_b200 import ops
+    nfeat, nhid, nclass = EPOCH_SHAPES[args.workload]
+    plan = ops.SpmmPlan(rp, ci, va, (n, n), device=device, assume_symmetric=True)
+    g = torch.Generator(device=device).manual_seed(15)
+    X = torch.randn(n, nfeat, device=device, generator=g)
+    labels = torch.randint(0, nclass, (n,), device=device, generator=g)
+    idx_train = torch.arange(n // 20, device=device)
+    torch.manual_seed(15)
+    net = gmodel.GCN(nfeat, nhid, nclass, dataset=args.workload, device=device, association=args.assoc)
+    net.features, net.adj_norm, net.labels = X, plan, labels
+    opt = torch.optim.Adam(net.parameters(), lr=net.lr, weight_decay=net.weight_decay)
+    step = lambda: net._step(opt, labels, idx_train)   # noqa: E731
+    steps = max(3, min(args.steps, 10))
+    ms_avg, ms_med, ms_min = time_steps(step, steps, 3, device)
+    torch.cuda.synchronize(device)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        loss = float(step()[1].item())
+    e2e_ms = (time.perf_counter() - t0) / steps * 1e3
+    return {"metric": "gcn_epoch_ms", "ms_per_epoch": ms_avg, "ms_median": ms_med, "ms_min": ms_min, "steps": steps,
+            "warmup": 3, "shape": f"{nfeat}->{nhid}->{nclass}", "association": args.assoc, "loss": loss,
+            "e2e_ms_per_epoch": e2e_ms,
+            "e2e": "GCN._step + loss.item() every epoch; features, labels and the plan resident as in the reference's fit()"}
+
+
+def epoch_object_multi(args, part, n, device, barrier):
+    """Same as epoch_object_single on the row partition (gcn_b200.dist.PartitionedGCN); max over ranks."""
+    import torch.distributed as dist
+    from gcn_b200 import dist as gdist
+    nfeat, nhid, nclass = EPOCH_SHAPES[args.workload]
+    g = torch.Generator(device=device).manual_seed(15 + part.rank)
+    X = torch.randn(part.m_local, nfeat, device=device, generator=g)
+    labels = torch.randint(0, nclass, (part.m_local,), device=device, generator=g)
+    n_train = n // 20
+    idx_train = torch.arange(max(0, min(part.hi, n_train) - part.lo), device=device)
+    net = gdist.PartitionedGCN(part, nfeat, nhid, nclass, association=args.assoc)
+    steps = max(3, min(args.steps, 10))
+    ms_avg, ms_med, ms_min = time_steps(lambda: net.step(X, labels, idx_train, n_train), steps, 3, device, barrier,
+                                        align=part._rank_barrier)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        loss = net.step(X, labels, idx_train, n_train).detach().clone()
+        dist.all_reduce(loss, group=part.group)
+        lv = float(loss.item())
+    barrier()
+    e2e_ms = (time.perf_counter() - t0) / steps * 1e3
+    t = torch.tensor([ms_avg, ms_med, ms_min, e2e_ms], device=device, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_avg, ms_med, ms_min, e2e_ms = t.tolist()
+    return {"metric": "gcn_epoch_ms", "ms_per_epoch": ms_avg, "ms_median": ms_med, "ms_min": ms_min, "steps": steps,
+            "warmup": 3, "shape": f"{nfeat}->{nhid}->{nclass}", "association": args.assoc, "loss": lv,
+            "e2e_ms_per_epoch": e2e_ms,
+            "e2e": "PartitionedGCN.step + all-reduced loss read back every epoch; max over ranks"}
 
 
 def run_epoch_single(args):
@@ -510,12 +754,68 @@ def run_epoch_multi(args):
                                             args.warmup, device, barrier, align=part._rank_barrier)
     t = torch.tensor([ms_avg, ms_med, ms_min], device=device, dtype=torch.float64)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    parity = None
+    if not args.no_parity:   # the exchange this epoch rides on, checked at the hidden width
+        parity = partition_parity_check(part, rp, ci, va, nhid, device, tol=1e-2 if args.wire == "bf16" else 1e-5)
     if rank == 0:
         ms_avg, ms_med, ms_min = t.tolist()
         print(json.dumps(epoch_line(args, name, n, nnz, world, ms_avg, ms_med, ms_min, clk.summary(),
-                                    {"gpu_launches": None, "parallelism": f"1-D row partition by nnz over {world} GPUs; "
+                                    {"gpu_launches": None, "parity_check": parity,
+                                     "parallelism": f"1-D row partition by nnz over {world} GPUs; "
                                      f"4 exchanges of the dense operand ({args.exchange}) + 1 gradient all-reduce per epoch"})))
     dist.destroy_process_group()
+    if parity is not None and not parity["ok"]:
+        raise SystemExit(f"bench.py: parity_check failed: {parity['max_rel_err']:.3e} > {parity['tol']}")
+
+
+def partition_parity_check(part, rp, ci, va, k, device, tol, steps=4, rows=256):
+    """Untimed self-check of the N-GPU path: `steps` consecutive partitioned SpMMs
+    under the REAL stream-ordered rank barrier (gcn_b200.dist._rank_barrier, an NCCL all-reduce), each with
+    a fresh operand (so that a stale exchange slot cannot pass; both slots are reused from step 3 on), and
+    `rows` sampled rows of this rank's result compared with an fp64 host evaluation of the same rows of
+    Â·B.  Returns {"max_rel_err", "rows", "steps", "tol", "ok"}, the error being the max over ranks of
+    max|C - C64| / max|C64|."""
+    import torch.distributed as dist
+    rank, world, stride, bounds = part.rank, part.world, part.stride, part.bounds
+    lo = part.lo
+    rng = np.random.default_rng(1234 + rank)
+    worst = 0.0
+    n_rows = 0
+    for s in range(steps):
+        g = torch.Generator(device=device).manual_seed(1000 * (s + 1) + rank)
+        B = torch.randn(part.m_local, k, device=device, generator=g)
+        slot = part.next_operand(k)
+        if slot is not None:        # fp32 pull mode: the producer writes into the free exchange slot
+            slot.copy_(B)
+            op = slot
+        else:
+            op = B
+        out = part.forward(op)
+        # every rank's operand, for the reference only: a plain NCCL all-gather of the padded blocks
+        padded = torch.zeros(stride, k, device=device)
+        padded[: part.m_local] = B
+        full = torch.empty(world * stride, k, device=device)
+        dist.all_gather_into_tensor(full, padded, group=part.group)
+        pick = np.sort(rng.choice(part.m_local, size=min(rows, part.m_local), replace=False))
+        got = out[torch.from_numpy(pick).to(device)].double().cpu().numpy()
+        ref = np.zeros((len(pick), k))
+        for i, r in enumerate(pick):
+            z0, z1 = int(rp[lo + r]), int(rp[lo + r + 1])
+            cols = ci[z0:z1].astype(np.int64)
+            owner = np.searchsorted(bounds, cols, side="right") - 1
+            pos = owner * stride + (cols - bounds[owner])
+            brow = full[torch.from_numpy(pos).to(device)].double().cpu().numpy()
+            ref[i] = va[z0:z1].astype(np.float64) @ brow
+        worst = max(worst, float(np.abs(got - ref).max() / max(np.abs(ref).max(), 1e-30)))
+        n_rows += len(pick)
+    t = torch.tensor([worst], device=device, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX, group=part.group)
+    cnt = torch.tensor([n_rows], device=device, dtype=torch.float64)
+    dist.all_reduce(cnt, op=dist.ReduceOp.SUM, group=part.group)
+    err = float(t.item())
+    return {"max_rel_err": err, "rows": int(cnt.item()), "steps": steps, "tol": tol, "ok": bool(err <= tol),
+            "barrier": "gcn_b200.dist._rank_barrier (stream-ordered NCCL all-reduce), fresh operand every step",
+            "reference": "fp64 host evaluation of the sampled rows of A·B"}
 
 
 def run_multi(args):
@@ -594,6 +894,12 @@ def run_multi(args):
         evs[2].record(); Ch.copy_(out_e, non_blocking=True)
         evs[3].record(); torch.cuda.synchronize(device)
         e2e_parts = [evs[i].elapsed_time(evs[i + 1]) for i in range(3)]
+    parity = None
+    if not args.no_parity:
+        parity = partition_parity_check(part, rp, ci, va, k, device, tol=1e-2 if args.wire == "bf16" else 1e-5)
+    epoch = None
+    if not args.no_epoch and args.workload in EPOCH_SHAPES:
+        epoch = epoch_object_multi(args, part, n, device, barrier)
     halo_rows = int(blocks["halo_row"].numel()) if args.exchange == "pull" else (world - 1) * part.stride
     t = torch.tensor([ms_avg, ms_med, ms_min, ph_local, ph_exch, ph_remote, halo_rows, e2e_ms], device=device,
                      dtype=torch.float64)
@@ -615,7 +921,10 @@ def run_multi(args):
             "config": {"workload": f"{name} SpMM C=A·B, k={k}, 1-D row partition by nnz over {world} GPUs, "
                                    + ("halo rows pulled over NVLink peer memory (gcnb_pull_rows)"
                                       if args.exchange == "pull" else "NCCL all-gather of B")
-                                   + " overlapped with the local-column block",
+                                   + " overlapped with the local-column block"
+                                   + ("; the operand is resident in the rank's exchange slot when the timed region "
+                                      "starts (where its producer, X·W, writes it: no publish copy in the step)"
+                                      if in_slot else ""),
                        "n": n, "nnz": nnz, "k": k, "exchange": args.exchange, "wire": args.wire,
                        "local_nnz_frac": stats[0].item() / max(nnz, 1),
                        "exchange_bytes_received_per_rank_max": gathered,
@@ -629,6 +938,7 @@ def run_multi(args):
                          "note": "aggregate: algorithmic bytes of the whole SpMM over N x per-GPU HBM peak; "
                                  "the step also moves allgather_bytes over NVLink"},
             "clocks": clk.summary(),
+            "parity_check": parity, "epoch": epoch,
             "e2e": None if args.no_e2e else {
                 "value": flops / (e2e_ms * 1e-3) / 1e9, "unit": UNIT, "h2d_bytes_per_step": n * k * 4,
                 "d2h_bytes_per_step": n * k * 4, "ms_per_step": e2e_ms,
@@ -637,6 +947,8 @@ def run_multi(args):
                        "the sum over ranks, time the max over ranks (wall clock between barriers)"},
         }))
     dist.destroy_process_group()
+    if parity is not None and not parity["ok"]:
+        raise SystemExit(f"bench.py: parity_check failed: {parity['max_rel_err']:.3e} > {parity['tol']}")
 
 
 def main():

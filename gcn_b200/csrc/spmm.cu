@@ -54,15 +54,15 @@ namespace gcnb {
 
 // non-zeros per stream segment: kSegNnz on large matrices, smaller when the matrix would not give
 // every SM a few dozen segments
-static int64_t seg_target(int64_t nnz) {
+static int64_t seg_target(int64_t nnz, int n_sm) {
   static const int64_t forced = getenv("GCNB_SEG_NNZ") ? atoll(getenv("GCNB_SEG_NNZ")) : 0;
   if (forced > 0) return forced;
-  const int64_t want = nnz / (148 * 64);
+  const int64_t want = nnz / ((int64_t)n_sm * 64);
   return std::max<int64_t>(64, std::min<int64_t>(kSegNnz, want));
 }
 
 static int upload_matrix(const int32_t* rowptr, const int32_t* col, const float* val, int64_t m,
-                         int64_t n, int64_t nnz, Matrix* M) {
+                         int64_t n, int64_t nnz, int n_sm, Matrix* M) {
   M->m = m; M->n = n; M->nnz = nnz;
   // block-class work lists (host, O(m))
   std::vector<WorkItem> items;
@@ -95,7 +95,7 @@ static int upload_matrix(const int32_t* rowptr, const int32_t* col, const float*
   std::vector<int32_t> s_split_rows, s_split_ptr;
   int64_t s_n_partials = 0;
   {
-    const int64_t seg_nnz = seg_target(nnz);
+    const int64_t seg_nnz = seg_target(nnz, n_sm);
     int64_t r0 = -1;
     auto close_run = [&](int64_t r_end) {
       if (r0 >= 0) segs.push_back({(int32_t)r0, (int32_t)r_end, rowptr[r0], rowptr[r_end]});
@@ -221,9 +221,12 @@ struct LaunchArgs {
 template <typename TB, int VEC, int NV, int U, int MINB>
 static void launch_stream_cfg(const LaunchArgs& a, int64_t gs, unsigned ytiles) {
   const Matrix& M = *a.M;
+  // GCNB_L2POL: bit 0 = (col,val) stream and C rows evict_first, bit 1 = feature rows evict_last
+  static const int l2pol = getenv("GCNB_L2POL") ? atoi(getenv("GCNB_L2POL")) : 1;
+  const int l2 = ((l2pol & 1) ? kL2Streams : 0) | ((l2pol & 2) ? kL2BLast : 0);
   spmm_stream_kernel<TB, VEC, NV, U, MINB><<<dim3((unsigned)gs, ytiles), kStreamWarps * 32, 0, a.stream>>>(
       M.segs, (int)M.n_segs, M.rowptr, M.cv, (const TB*)a.B, (uint32_t)(a.ldb * sizeof(TB)), a.C, a.ldc,
-      a.partials, a.k, a.bias, a.epi);
+      a.partials, a.k, a.bias, a.epi | l2);
 }
 
 template <typename TB, int VEC, int NV>
@@ -486,7 +489,7 @@ int gcnb_plan_create(const int32_t* rowptr, const int32_t* col, const float* val
   if (!p) return set_error(GCNB_ERR_ALLOC, "out of host memory");
   p->device = device;
   p->n_sm = sm_count(device);
-  rc = upload_matrix(rowptr, col, val, m, n, nnz, &p->a);
+  rc = upload_matrix(rowptr, col, val, m, n, nnz, p->n_sm, &p->a);
   if (rc != GCNB_OK) { gcnb_plan_destroy(p); return rc; }
 
   if (flags & GCNB_PLAN_ASSUME_SYMMETRIC) {
@@ -501,7 +504,7 @@ int gcnb_plan_create(const int32_t* rowptr, const int32_t* col, const float* val
                       memcmp(t_val.data(), val, (size_t)nnz * 4) == 0))) {
       p->symmetric = true;  // bit-identical transpose: A^T·dY can run on A
     } else {
-      rc = upload_matrix(t_rowptr.data(), t_col.data(), t_val.data(), n, m, nnz, &p->at);
+      rc = upload_matrix(t_rowptr.data(), t_col.data(), t_val.data(), n, m, nnz, p->n_sm, &p->at);
       if (rc != GCNB_OK) { gcnb_plan_destroy(p); return rc; }
       p->has_t = true;
     }

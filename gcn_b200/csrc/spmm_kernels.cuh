@@ -54,6 +54,37 @@ __device__ __forceinline__ int2 ld_stream_int2(const int2* p) {
   return r;
 }
 
+// L2 eviction priorities (createpolicy + .L2::cache_hint; the policy rides in the memory descriptor, so a
+// hinted access costs no extra instruction).  The (col,val) stream and the C rows are touched once:
+// evict_first keeps them from pushing the re-used feature rows out of the 126 MB L2.
+__device__ __forceinline__ uint64_t l2_policy(int kind) {   // 0 normal, 1 evict_first, 2 evict_last
+  uint64_t pol;
+  if (kind == 1) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  else if (kind == 2) asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  else asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ int2 ld_stream_int2(const int2* p, uint64_t pol) {
+  int2 r;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.s32 {%0, %1}, [%2], %3;"
+               : "=r"(r.x), "=r"(r.y)
+               : "l"(p), "l"(pol));
+  return r;
+}
+__device__ __forceinline__ void ldg_hint(const void* p, uint64_t pol, uint4& v) {
+  asm volatile("ld.global.nc.L2::cache_hint.v4.b32 {%0, %1, %2, %3}, [%4], %5;"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p), "l"(pol));
+}
+__device__ __forceinline__ void ldg_hint(const void* p, uint64_t pol, uint2& v) {
+  asm volatile("ld.global.nc.L2::cache_hint.v2.b32 {%0, %1}, [%2], %3;" : "=r"(v.x), "=r"(v.y) : "l"(p), "l"(pol));
+}
+__device__ __forceinline__ void ldg_hint(const void* p, uint64_t pol, uint32_t& v) {
+  asm volatile("ld.global.nc.L2::cache_hint.b32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol));
+}
+__device__ __forceinline__ void ldg_hint(const void* p, uint64_t pol, unsigned short& v) {
+  asm volatile("ld.global.nc.L2::cache_hint.u16 %0, [%1], %2;" : "=h"(v) : "l"(p), "l"(pol));
+}
+
 template <typename TB, int VEC>
 struct VecLoad;
 
@@ -129,6 +160,18 @@ template <int VEC>
 struct RawVec<float, VEC> {
   float w[VEC];
   __device__ __forceinline__ void load(const float* p) { VecLoad<float, VEC>::load(p, w); }
+  __device__ __forceinline__ void load(const float* p, uint64_t pol) {
+    if constexpr (VEC == 4) {
+      uint4 v; ldg_hint(p, pol, v);
+      w[0] = __uint_as_float(v.x); w[1] = __uint_as_float(v.y); w[2] = __uint_as_float(v.z); w[3] = __uint_as_float(v.w);
+    } else if constexpr (VEC == 2) {
+      uint2 v; ldg_hint(p, pol, v);
+      w[0] = __uint_as_float(v.x); w[1] = __uint_as_float(v.y);
+    } else {
+      uint32_t v; ldg_hint(p, pol, v);
+      w[0] = __uint_as_float(v);
+    }
+  }
   __device__ __forceinline__ void zero() {
 #pragma unroll
     for (int x = 0; x < VEC; ++x) w[x] = 0.f;
@@ -142,6 +185,7 @@ template <>
 struct RawVec<__nv_bfloat16, 8> {
   uint4 w;
   __device__ __forceinline__ void load(const __nv_bfloat16* p) { w = __ldg(reinterpret_cast<const uint4*>(p)); }
+  __device__ __forceinline__ void load(const __nv_bfloat16* p, uint64_t pol) { ldg_hint(p, pol, w); }
   __device__ __forceinline__ void zero() { w = make_uint4(0, 0, 0, 0); }
   __device__ __forceinline__ void get(float (&o)[8]) const {
     bf16x2_to_f32(w.x, o[0], o[1]); bf16x2_to_f32(w.y, o[2], o[3]);
@@ -152,6 +196,7 @@ template <>
 struct RawVec<__nv_bfloat16, 4> {
   uint2 w;
   __device__ __forceinline__ void load(const __nv_bfloat16* p) { w = __ldg(reinterpret_cast<const uint2*>(p)); }
+  __device__ __forceinline__ void load(const __nv_bfloat16* p, uint64_t pol) { ldg_hint(p, pol, w); }
   __device__ __forceinline__ void zero() { w = make_uint2(0, 0); }
   __device__ __forceinline__ void get(float (&o)[4]) const {
     bf16x2_to_f32(w.x, o[0], o[1]); bf16x2_to_f32(w.y, o[2], o[3]);
@@ -161,6 +206,7 @@ template <>
 struct RawVec<__nv_bfloat16, 2> {
   uint32_t w;
   __device__ __forceinline__ void load(const __nv_bfloat16* p) { w = __ldg(reinterpret_cast<const uint32_t*>(p)); }
+  __device__ __forceinline__ void load(const __nv_bfloat16* p, uint64_t pol) { ldg_hint(p, pol, w); }
   __device__ __forceinline__ void zero() { w = 0; }
   __device__ __forceinline__ void get(float (&o)[2]) const { bf16x2_to_f32(w, o[0], o[1]); }
 };
@@ -168,6 +214,7 @@ template <>
 struct RawVec<__nv_bfloat16, 1> {
   unsigned short w;
   __device__ __forceinline__ void load(const __nv_bfloat16* p) { w = __ldg(reinterpret_cast<const unsigned short*>(p)); }
+  __device__ __forceinline__ void load(const __nv_bfloat16* p, uint64_t pol) { ldg_hint(p, pol, w); }
   __device__ __forceinline__ void zero() { w = 0; }
   __device__ __forceinline__ void get(float (&o)[1]) const { o[0] = __uint_as_float(((uint32_t)w) << 16); }
 };
@@ -183,6 +230,21 @@ __device__ __forceinline__ void store_vec(float* p, const float (&v)[VEC]) {
     __stcs(reinterpret_cast<float2*>(p), make_float2(v[0], v[1]));
   } else {
     __stcs(p, v[0]);
+  }
+}
+
+template <int VEC>
+__device__ __forceinline__ void store_vec(float* p, const float (&v)[VEC], uint64_t pol) {
+  if constexpr (VEC % 4 == 0) {
+#pragma unroll
+    for (int i = 0; i < VEC; i += 4)
+      asm volatile("st.global.L1::no_allocate.L2::cache_hint.v4.f32 [%0], {%1, %2, %3, %4}, %5;"
+                   ::"l"(p + i), "f"(v[i]), "f"(v[i + 1]), "f"(v[i + 2]), "f"(v[i + 3]), "l"(pol) : "memory");
+  } else if constexpr (VEC == 2) {
+    asm volatile("st.global.L1::no_allocate.L2::cache_hint.v2.f32 [%0], {%1, %2}, %3;"
+                 ::"l"(p), "f"(v[0]), "f"(v[1]), "l"(pol) : "memory");
+  } else {
+    asm volatile("st.global.L1::no_allocate.L2::cache_hint.f32 [%0], %1, %2;" ::"l"(p), "f"(v[0]), "l"(pol) : "memory");
   }
 }
 
@@ -512,6 +574,8 @@ spmm_warp_row_kernel(const int32_t* __restrict__ rowptr, const int2* __restrict_
 //     load, prefetched one slab ahead, read back as LDS broadcasts).
 // Every output row is still produced by exactly one warp: no atomics, bit-reproducible.
 constexpr int kStreamWarps = 4;
+constexpr int kL2Streams = 0x100;   // stream-kernel argument bits above the GCNB_EPI_* flags
+constexpr int kL2BLast = 0x200;
 constexpr int kSegNnz = 768;     // target non-zeros per segment of short rows (plan time)
 constexpr int kSegLong = 1024;   // a long row is cut into pieces of at most this many non-zeros
 
@@ -528,8 +592,13 @@ __global__ void __launch_bounds__(kStreamWarps * 32, MINB)
 spmm_stream_kernel(const Seg* __restrict__ segs, int n_segs, const int32_t* __restrict__ rowptr,
                    const int2* __restrict__ cv, const TB* __restrict__ B, uint32_t ldb_bytes,
                    float* __restrict__ C, int64_t ldc, float* __restrict__ partials, int k,
-                   const float* __restrict__ bias, int epi_arg) {
+                   const float* __restrict__ bias, int epi_l2) {
   static_assert(32 % U == 0, "ring size must divide the slab");
+  // bits 8.. of the last argument: L2 eviction priorities (kL2Streams: (col,val) stream and C rows are
+  // evict_first; kL2BLast: gathered feature rows are evict_last), chosen by the host (spmm.cu)
+  const int epi_arg = epi_l2 & 0xff;
+  const uint64_t pol_s = l2_policy((epi_l2 & kL2Streams) ? 1 : 0);
+  const uint64_t pol_b = l2_policy((epi_l2 & kL2BLast) ? 2 : 0);
   __shared__ alignas(16) int2 s_cv[kStreamWarps][32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int s = blockIdx.x * kStreamWarps + warp;
@@ -597,7 +666,7 @@ spmm_stream_kernel(const Seg* __restrict__ segs, int n_segs, const int32_t* __re
         }
 #pragma unroll
         for (int x = 0; x < VEC; ++x) o[x] = epilogue(acc[t][x], bias, coff[t] + x, epi);
-        store_vec<VEC>(crow + coff[t], o);
+        store_vec<VEC>(crow + coff[t], o, pol_s);
       }
 #pragma unroll
       for (int x = 0; x < VEC; ++x) acc[t][x] = 0.f;
@@ -644,19 +713,19 @@ spmm_stream_kernel(const Seg* __restrict__ segs, int n_segs, const int32_t* __re
   // issue side: `nxt` = stream position of the next non-zero to gather; its slab is refilled whenever
   // nxt crosses a multiple of 32 (every earlier entry of the old slab has been issued by then)
   int2 e = make_int2(0, 0);
-  if (lane < total) e = ld_stream_int2(src + lane);
+  if (lane < total) e = ld_stream_int2(src + lane, pol_s);
   auto refill = [&](int at) {   // make slab hold stream positions [at, at+32)
     __syncwarp();
     asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(slab_l), "r"(e.x), "r"(e.y) : "memory");
     __syncwarp();
-    if (at + 32 + lane < total) e = ld_stream_int2(src + at + 32 + lane);
+    if (at + 32 + lane < total) e = ld_stream_int2(src + at + 32 + lane, pol_s);
   };
   auto gather = [&](int u, int c, int vbits) {
     av[u] = __int_as_float(vbits);
     const char* p0 = bl + (uint64_t)(uint32_t)c * ldb_bytes;
 #pragma unroll
     for (int t = 0; t < NV; ++t)
-      if (cok[t]) bv[u][t].load(reinterpret_cast<const TB*>(p0) + t * 32 * VEC);
+      if (cok[t]) bv[u][t].load(reinterpret_cast<const TB*>(p0) + t * 32 * VEC, pol_b);
   };
   auto issue = [&](int u, int at) {   // gather non-zero `at` (valid) into ring slot u
     int2 q;

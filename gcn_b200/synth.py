@@ -9,7 +9,8 @@ gcn6.py:302-312).  Values are computed in fp64 and cast to fp32 like the referen
 Shapes (undirected edge counts before the self-loops are added):
   cora      n=2 708        5 278 edges    Erdős–Rényi pairs
   arxiv     n=169 343      1 166 243      random pairs, symmetrised
-  reddit    n=232 965      57.3 M         Chung-Lu power law (exponent 2.1)
+  reddit    n=232 965      57.3 M         Chung-Lu power law (exponent 2.1), 57.3 M DISTINCT pairs
+                                          (nnz(Â) = 2·57.3 M + n = 114.8 M, the "114 M edges" of the shape)
   products  n=2 449 029    61.86 M        power-law degrees, community-local endpoints (see
                                           `local_powerlaw`): co-purchase graphs are strongly
                                           clustered; ids are community-contiguous
@@ -57,9 +58,34 @@ def edges_er(n, edges, device, seed=SEED):
 
 
 def edges_chung_lu(n, edges, exponent, device, seed=SEED):
+    """`edges` DISTINCT undirected non-loop pairs with Chung-Lu (power-law weight) endpoints.
+
+    Sampling with replacement loses a large share of the pairs as duplicates on a hub-heavy sequence
+    (exponent 2.1, n = 233 k: 57.3 M samples leave 34 M distinct pairs, i.e. a graph 40 % smaller than
+    the shape names — round-1 VERDICT item 4), so pairs are drawn in rounds until enough distinct ones
+    exist and the surplus is dropped uniformly at random."""
     g = _gen(device, seed)
     cdf = _powerlaw_cdf(n, exponent, device, g)
-    return _sample(cdf, edges, g), _sample(cdf, edges, g)
+    keys = torch.empty(0, dtype=torch.int64, device=device)
+    draw = edges
+    for _round in range(64):
+        a, b = _sample(cdf, draw, g), _sample(cdf, draw, g)
+        lo, hi = torch.minimum(a, b), torch.maximum(a, b)
+        keep = lo != hi
+        keys = torch.unique(torch.cat((keys, lo[keep] * n + hi[keep])))
+        del a, b, lo, hi, keep
+        if keys.numel() >= edges:
+            break
+        # the yield of a round falls as the hub pairs fill up: draw the shortfall times the inverse of
+        # the last yield (bounded), so that a handful of rounds suffices
+        draw = int(min(4 * edges, max(edges // 8, 2.5 * (edges - keys.numel()))))
+    if keys.numel() < edges:
+        raise RuntimeError(f"chung_lu: only {keys.numel()} distinct pairs of {edges} after 64 rounds")
+    if keys.numel() > edges:
+        pick = torch.randperm(keys.numel(), device=device, generator=g)[:edges]
+        keys = keys[pick]
+    src = torch.div(keys, n, rounding_mode="floor")
+    return src, keys - src * n
 
 
 def edges_local_powerlaw(n, edges, exponent, p_local, window, device, seed=SEED):
