@@ -3,6 +3,8 @@
 // reference's names and argument orders, renumber.cu:23,157,233 and tile.cu:11-12).
 #include <stdio.h>
 
+#include <exception>
+#include <new>
 #include <vector>
 
 #include "../common.h"
@@ -41,30 +43,37 @@ static void invert_rank(const std::vector<int64_t>& rank, int32_t* vomp) {
   for (size_t old = 0; old < rank.size(); ++old) vomp[rank[old]] = (int32_t)old;
 }
 
+// C++ exceptions (std::bad_alloc from the work vectors, std::system_error from the host threads of
+// parallel_rows) must not cross the C ABI: every entry point is a function-try-block.
+#define GCNB_CATCH_ALL                                                                       \
+  catch (const std::bad_alloc&) { return set_error(GCNB_ERR_ALLOC, "out of host memory"); }  \
+  catch (const std::exception& e) { return set_error(GCNB_ERR_ALLOC, "host exception: %s", e.what()); } \
+  catch (...) { return set_error(GCNB_ERR_ALLOC, "unknown host exception"); }
+
 extern "C" {
 
 int gcnb_order_deg(const int32_t* rowptr, const int32_t* col, int64_t m, int64_t nnz, int desc,
-                   int64_t* rank_out) {
+                   int64_t* rank_out) try {
   int rc = check_csr(rowptr, col, m, nnz);
   if (rc != GCNB_OK) return rc;
   GCNB_REQUIRE(rank_out != nullptr || m == 0, "rank_out is null");
   const std::vector<int64_t> r = order_deg({rowptr, col, m, nnz}, desc != 0);
   for (int64_t i = 0; i < m; ++i) rank_out[i] = r[i];
   return GCNB_OK;
-}
+} GCNB_CATCH_ALL
 
 int gcnb_order_rcm(const int32_t* rowptr, const int32_t* col, int64_t m, int64_t nnz,
-                   int64_t* rank_out) {
+                   int64_t* rank_out) try {
   int rc = check_csr(rowptr, col, m, nnz);
   if (rc != GCNB_OK) return rc;
   GCNB_REQUIRE(rank_out != nullptr || m == 0, "rank_out is null");
   const std::vector<int64_t> r = order_rcm({rowptr, col, m, nnz});
   for (int64_t i = 0; i < m; ++i) rank_out[i] = r[i];
   return GCNB_OK;
-}
+} GCNB_CATCH_ALL
 
 int gcnb_order_gorder(const int32_t* rowptr, const int32_t* col, int64_t m, int64_t nnz,
-                      int window, int64_t* rank_out) {
+                      int window, int64_t* rank_out) try {
   int rc = check_csr(rowptr, col, m, nnz);
   if (rc != GCNB_OK) return rc;
   GCNB_REQUIRE(rank_out != nullptr || m == 0, "rank_out is null");
@@ -76,10 +85,10 @@ int gcnb_order_gorder(const int32_t* rowptr, const int32_t* col, int64_t m, int6
                      "reference is undefined on isolated vertices (unitheap.cu:31-33)");
   for (int64_t i = 0; i < m; ++i) rank_out[i] = r[i];
   return GCNB_OK;
-}
+} GCNB_CATCH_ALL
 
 int gcnb_perm_apply(int32_t* rowptr, int32_t* col, float* val, const int32_t* vomp, int64_t m,
-                    int64_t nnz) {
+                    int64_t nnz) try {
   int rc = check_csr(rowptr, col, m, nnz);
   if (rc != GCNB_OK) return rc;
   GCNB_REQUIRE(nnz == 0 || val != nullptr, "val is null");
@@ -87,7 +96,7 @@ int gcnb_perm_apply(int32_t* rowptr, int32_t* col, float* val, const int32_t* vo
   if (rc != GCNB_OK) return rc;
   perm_apply(rowptr, col, val, vomp, m, nnz);
   return GCNB_OK;
-}
+} GCNB_CATCH_ALL
 
 static int renumber_with_rank(int32_t* rowptr, int32_t* col, float* val, int32_t* vomp, int64_t m,
                               int64_t nnz, const std::vector<int64_t>& rank) {
@@ -98,7 +107,7 @@ static int renumber_with_rank(int32_t* rowptr, int32_t* col, float* val, int32_t
 }
 
 int gcnb_renumber_gorder(int32_t* rowptr, int32_t* col, float* val, int32_t* vomp, int64_t m,
-                         int64_t nnz, int window) {
+                         int64_t nnz, int window) try {
   int rc = check_csr(rowptr, col, m, nnz);
   if (rc != GCNB_OK) return rc;
   GCNB_REQUIRE(window >= 1, "window = %d must be >= 1", window);
@@ -106,56 +115,56 @@ int gcnb_renumber_gorder(int32_t* rowptr, int32_t* col, float* val, int32_t* vom
   if (!order_gorder({rowptr, col, m, nnz}, window, &r))
     return set_error(GCNB_ERR_UNSUPPORTED, "Gorder needs every vertex to have an edge");
   return renumber_with_rank(rowptr, col, val, vomp, m, nnz, r);
-}
+} GCNB_CATCH_ALL
 
 int gcnb_renumber_rcm(int32_t* rowptr, int32_t* col, float* val, int32_t* vomp, int64_t m,
-                      int64_t nnz) {
+                      int64_t nnz) try {
   int rc = check_csr(rowptr, col, m, nnz);
   if (rc != GCNB_OK) return rc;
   return renumber_with_rank(rowptr, col, val, vomp, m, nnz, order_rcm({rowptr, col, m, nnz}));
-}
+} GCNB_CATCH_ALL
 
 int gcnb_renumber_deg(int32_t* rowptr, int32_t* col, float* val, int32_t* vomp, int64_t m,
-                      int64_t nnz, int desc) {
+                      int64_t nnz, int desc) try {
   int rc = check_csr(rowptr, col, m, nnz);
   if (rc != GCNB_OK) return rc;
   return renumber_with_rank(rowptr, col, val, vomp, m, nnz,
                             order_deg({rowptr, col, m, nnz}, desc != 0));
-}
+} GCNB_CATCH_ALL
 
 int gcnb_renumber_dfs(int32_t* rowptr, int32_t* col, float* val, int32_t* vomp, int64_t m,
-                      int64_t nnz) {
+                      int64_t nnz) try {
   int rc = check_csr(rowptr, col, m, nnz);
   if (rc != GCNB_OK) return rc;
   GCNB_REQUIRE(vomp != nullptr || m == 0, "vomp is null");
   dfs_order({rowptr, col, m, nnz}, vomp);
   perm_apply(rowptr, col, val, vomp, m, nnz);
   return GCNB_OK;
-}
+} GCNB_CATCH_ALL
 
 int gcnb_renumber_rabbit(int32_t* rowptr, int32_t* col, float* val, int32_t* vomp, int64_t m,
-                         int64_t nnz) {
+                         int64_t nnz) try {
   int rc = check_csr(rowptr, col, m, nnz);
   if (rc != GCNB_OK) return rc;
   GCNB_REQUIRE(vomp != nullptr || m == 0, "vomp is null");
   rabbit_order({rowptr, col, m, nnz}, vomp);
   perm_apply(rowptr, col, val, vomp, m, nnz);
   return GCNB_OK;
-}
+} GCNB_CATCH_ALL
 
 int gcnb_tile_count(const int32_t* rowptr, const int32_t* col, int64_t m, int64_t nnz, int tm,
-                    int64_t* n_segs_out) {
+                    int64_t* n_segs_out) try {
   GCNB_REQUIRE(rowptr && (nnz == 0 || col) && n_segs_out, "null pointer");
   GCNB_REQUIRE(tm >= 1 && tm <= 64, "tm = %d out of range", tm);
   GCNB_REQUIRE(m >= 0 && rowptr[m] == nnz, "rowptr[m] != nnz");
   *n_segs_out = build_segments(rowptr, col, nullptr, m, tm, 0, (m + tm - 1) / tm, 0, true, nullptr);
   return GCNB_OK;
-}
+} GCNB_CATCH_ALL
 
 int gcnb_csr2tile(const int32_t* rowptr, const int32_t* col, const float* val, int64_t m,
                   int64_t n, int64_t nnz, int tm, int n_sm, int32_t* segVoMap,
                   int32_t* seg_rowPtr, float* segNzCV, int32_t* grouped_tailSeg,
-                  int32_t* next_seg, int64_t* n_segs_out) {
+                  int32_t* next_seg, int64_t* n_segs_out) try {
   (void)n;
   GCNB_REQUIRE(rowptr && (nnz == 0 || (col && val)) && n_segs_out, "null pointer");
   GCNB_REQUIRE(segVoMap && seg_rowPtr && (nnz == 0 || segNzCV), "null output pointer");
@@ -170,7 +179,7 @@ int gcnb_csr2tile(const int32_t* rowptr, const int32_t* col, const float* val, i
   if (next_seg) build_buckets(seg_rowPtr, n_segs, nnz, tm, n_sm, grouped_tailSeg, next_seg);
   *n_segs_out = n_segs;
   return GCNB_OK;
-}
+} GCNB_CATCH_ALL
 
 // ---- compat: reference names (void, errors to stderr + gcnb_last_error) -------------------------
 static void report(const char* fn, int rc) {

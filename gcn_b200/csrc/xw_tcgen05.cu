@@ -36,6 +36,8 @@
 
 #include <algorithm>
 
+#include <atomic>
+
 #include "common.h"
 
 namespace gcnb {
@@ -470,11 +472,16 @@ namespace {
 
 template <int BN, int MODE, bool BRAW>
 int launch_main(const xw::Params& p, int64_t tiles, int splits, cudaStream_t stream) {
-  static bool configured = false;   // benign race: the attribute is idempotent
-  if (!configured) {
+  // the > 48 KB shared-memory opt-in is a per-DEVICE attribute of the function: one bit per device
+  // ordinal (a process may call gcnb_xw on cuda:1 after cuda:0).  Benign race: the attribute is idempotent.
+  static std::atomic<uint64_t> configured{0};
+  int dev = 0;
+  GCNB_CHECK_CUDA(cudaGetDevice(&dev));
+  const uint64_t bit = 1ull << (dev & 63);
+  if (dev >= 64 || !(configured.load(std::memory_order_relaxed) & bit)) {
     GCNB_CHECK_CUDA(cudaFuncSetAttribute(xw::xw_kernel<BN, MODE, BRAW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          xw::smem_bytes(BN, BRAW)));
-    configured = true;
+    configured.fetch_or(bit, std::memory_order_relaxed);
   }
   xw::xw_kernel<BN, MODE, BRAW>
       <<<dim3((unsigned)tiles, (unsigned)splits), xw::THREADS, xw::smem_bytes(BN, BRAW), stream>>>(p);

@@ -417,10 +417,10 @@ class PartitionedGCN(torch.nn.Module):
         nfeat, nhid = self.gc1.weight.shape
         nclass = self.gc2.weight.shape[1]
         if self.association == "auto" and nfeat <= nhid:
-            if self._ax is None or self._ax[0] != x_local.data_ptr():
+            if self._ax is None or self._ax[0] is not x_local or self._ax[1] != x_local._version:
                 with torch.no_grad():   # Â·X once: X is constant over the epochs
-                    self._ax = (x_local.data_ptr(), self.part.forward(x_local))
-            h = gemm.xw(self._ax[1], self.gc1.weight, bias=self.gc1.bias, relu=True)
+                    self._ax = (x_local, x_local._version, self.part.forward(x_local))
+            h = gemm.xw(self._ax[2], self.gc1.weight, bias=self.gc1.bias, relu=True)
         else:
             support = gemm.xw(x_local, self.gc1.weight, out=self.part.next_operand(nhid))   # straight into the exchange slot
             h = torch.relu(spmm(self.part, support) + self.gc1.bias)

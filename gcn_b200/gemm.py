@@ -65,8 +65,16 @@ def gemm_raw(A: torch.Tensor, B: torch.Tensor, trans_a=False, trans_b=False, bia
 class _XW(torch.autograd.Function):
     @staticmethod
     def forward(ctx, X, W, bias, relu, precision, out=None):
-        if out is not None and relu:
-            raise ValueError("gemm.xw: `out` cannot be combined with relu (the result is kept for backward)")
+        if out is not None:
+            if relu:
+                raise ValueError("gemm.xw: `out` cannot be combined with relu (the result is kept for backward)")
+            if (out.dtype != torch.float32 or out.device != X.device or out.dim() != 2 or out.stride(1) != 1
+                    or tuple(out.shape) != (X.shape[0], W.shape[1])):
+                raise ValueError("gemm.xw: `out` must be a float32 (M, N) tensor on the operands' device with "
+                                 "contiguous rows")
+            # (no ctx.mark_dirty: `out` is a scratch destination that carries no history — typically a slice of
+            # an exchange slot — and marking a view dirty re-bases its autograd history onto the slot's base
+            # tensor, which cuts the gradient path to X and W)
         out = gemm_raw(X.detach(), W.detach(), bias=None if bias is None else bias.detach(),
                        relu=relu, precision=precision, out=out)
         ctx.relu = relu

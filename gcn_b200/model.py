@@ -51,7 +51,7 @@ class GCN(nn.Module):
         if association not in ("reference", "auto"):
             raise ValueError("association must be 'reference' or 'auto'")
         self.association = association
-        self._ax_cache = None   # (features data_ptr, id(adj), Â·X)
+        self._ax_cache = None   # (features tensor, its _version, adjacency object, Â·X): strong references
         self.device = torch.device(device)
         self.nfeat = nfeat
         self.hidden_sizes = [nhid]
@@ -91,11 +91,13 @@ class GCN(nn.Module):
         self._ax_cache = None
 
     def _aggregated_features(self, x, adj):
-        key = (x.data_ptr(), id(adj))
-        if self._ax_cache is None or self._ax_cache[:2] != key:
+        # the cache holds the tensor and the adjacency themselves (an address or id() can be re-used by a
+        # new object once the old one is freed) and the tensor's version counter (in-place edits)
+        c = self._ax_cache
+        if c is None or c[0] is not x or c[1] != x._version or c[2] is not adj:
             with torch.no_grad():
-                self._ax_cache = key + (ops.plan_for(adj).spmm(x),)
-        return self._ax_cache[2]
+                self._ax_cache = (x, x._version, adj, ops.plan_for(adj).spmm(x))
+        return self._ax_cache[3]
 
     def _forward_min_width(self, x, adj):
         nfeat, nhid = self.gc1.weight.shape
@@ -324,6 +326,7 @@ class GCN(nn.Module):
         """Log-probabilities in the (possibly reordered) vertex numbering of the last ``fit``."""
         self.eval()
         if features is not None or adj is not None:
+            self._ax_cache = None
             labels = self.labels if self.labels is not None else np.zeros(features.shape[0], dtype=np.int64)
             self.features, self.adj_norm, _, self.vomp = self._prepare(features, adj, labels, True, None)
         return self.forward(self.features, self.adj_norm)

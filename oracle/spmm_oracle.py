@@ -122,6 +122,14 @@ def gcn_layer_cpu(adj_coo, x, weight, bias=None):
     return out + bias if bias is not None else out
 
 
+def gcn_layer2_cpu(adj_coo, x, weight, bias=None):
+    """GraphConvolution2.forward of the reference on CPU (pygcn/gcn5.py:134-139; flex form gcn6.py:184-194):
+    support = spmm(adj, input); output = mm(support, W); + bias."""
+    import torch
+    out = torch.mm(torch.spmm(adj_coo, x), weight)
+    return out + bias if bias is not None else out
+
+
 def gcn_epoch_cpu(adj_coo, x, labels, idx_train, params, optimizer, dropout=0.5):
     """One training epoch of the reference's 2-layer GCN on the host cores, restated from
     pygcn/gcn1.py:62-118 (model: gc1 = A·(X·W1)+b1, ReLU, dropout, gc2 = A·(H·W2)+b2, log_softmax) and

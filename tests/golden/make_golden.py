@@ -15,7 +15,8 @@ Sources of every stored answer (nothing here is computed by gcn_b200 or by oracl
     order_deg.cu, order_rcm.cu, order_gorder.cu, renumber.cu dfs/gorder/perm_apply);
   * tile metadata: compiled tile.cu, as shipped (n_segs, segVoMap) and with the one-token
     tile.cu:71 correction (seg_rowPtr, segNzCV) — SURVEY.md §8c;
-  * GCN: pygcn.gcn1.GCN forward + backward on CPU with dropout disabled (Cora-shaped).
+  * GCN: pygcn.gcn1.GCN forward + backward on CPU with dropout disabled (Cora-shaped);
+  * (Â·X)·W + b layer: pygcn.gcn5.GraphConvolution2 forward + backward on CPU (gc2_powerlaw.npz).
 The fixtures travel to the GPU box; /root/reference does not.
 """
 import os
@@ -147,10 +148,45 @@ def gcn_case():
     print("gcn_cora loss", loss.item())
 
 
+def gc2_case():
+    """(Â·X)·W + b forward and backward by EXECUTING the reference's own layer class
+    pygcn.gcn5.GraphConvolution2 (pygcn/gcn5.py:101-139: torch.spmm(adj, input), torch.mm(support, W),
+    + bias) on CPU.  gcn5 loads './cuspmm.so' relative to the working directory at import
+    (gcn5.py:18), so the import happens inside oracle/_ref/, where our recipe built that file."""
+    cwd = os.getcwd()
+    os.chdir(os.path.join(ROOT, "oracle", "_ref"))
+    try:
+        from pygcn import gcn5
+    finally:
+        os.chdir(cwd)
+    rng = np.random.default_rng(SEED + 2)
+    n, nin, nout = 777, 52, 24          # ragged sizes: n % 8 != 0, widths that are multiples of 4 only
+    a = pattern("powerlaw", n, 6000, rng)
+    adj = ref_utils.sparse_mx_to_torch_sparse_tensor(ref_utils.normalize_adj(a)).coalesce()
+    torch.manual_seed(SEED)
+    layer = gcn5.GraphConvolution2(nin, nout)
+    x = torch.from_numpy(rng.standard_normal((n, nin)).astype(np.float32)).requires_grad_(True)
+    out = layer(x, adj)
+    g = torch.from_numpy(rng.standard_normal((n, nout)).astype(np.float32))
+    out.backward(g)
+    an = adj.coalesce()
+    np.savez_compressed(
+        os.path.join(OUT, "gc2_powerlaw.npz"),
+        adj_idx=an.indices().numpy(), adj_val=an.values().numpy(), n=np.int64(n),
+        x=x.detach().numpy(), W=layer.weight.detach().numpy(), b=layer.bias.detach().numpy(),
+        out=out.detach().numpy(), gout=g.numpy(), gx=x.grad.numpy(),
+        gW=layer.weight.grad.numpy(), gb=layer.bias.grad.numpy())
+    print("gc2_powerlaw out", float(out.abs().max()))
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "gc2":     # only the fixture added in round 2
+        gc2_case()
+        sys.exit(0)
     graph_case("er_small", "er", 96, 300, 16, 1)
     graph_case("er_ragged", "er", 203, 700, 7, 2)       # m % 8 != 0, odd k
     graph_case("powerlaw", "powerlaw", 400, 4000, 32, 3)
     graph_case("banded", "banded", 512, 3000, 100, 4)    # k = 100 (products width)
     graph_case("star", "star", 1500, 1300, 47, 5)        # a 1300-nnz row: block class + split segments
     gcn_case()
+    gc2_case()

@@ -66,6 +66,30 @@ def test_layer_api_matches_reference_signature(golden_gcn):
     assert l2.bias is None and rel_err(out2.detach().cpu().numpy(), ref2.detach().cpu().numpy()) < 1e-4
 
 
+def test_graphconvolution2_matches_reference_layer():
+    """§8 a2: (Â·X)·W + b forward AND backward against tests/golden/gc2_powerlaw.npz, which holds what the
+    reference's own class pygcn.gcn5.GraphConvolution2 (gcn5.py:101-139) produced on CPU (make_golden.py
+    gc2_case).  North-star tolerance: 1e-5 on the output, 2e-5 on the gradients (as for a1)."""
+    from conftest import load_golden
+    g = load_golden("gc2_powerlaw")
+    n = int(g["n"])
+    adj = torch.sparse_coo_tensor(g["adj_idx"], g["adj_val"], (n, n)).coalesce().to(DEV)
+    layer = layers.GraphConvolution2(g["W"].shape[0], g["W"].shape[1]).to(DEV)
+    with torch.no_grad():
+        layer.weight.copy_(torch.from_numpy(g["W"]))
+        layer.bias.copy_(torch.from_numpy(g["b"]))
+    x = torch.from_numpy(g["x"]).to(DEV).requires_grad_(True)
+    out = layer(x, adj)
+    out.backward(torch.from_numpy(g["gout"]).to(DEV))
+    assert rel_err(out.detach().cpu().numpy(), g["out"]) < TOL
+    assert rel_err(x.grad.cpu().numpy(), g["gx"]) < 2e-5
+    assert rel_err(layer.weight.grad.cpu().numpy(), g["gW"]) < 2e-5
+    assert rel_err(layer.bias.grad.cpu().numpy(), g["gb"]) < 2e-5
+    # the fused-ReLU form used by GCN.forward: same numbers, clamped
+    out_r = layer(x.detach(), adj, relu=True)
+    assert rel_err(out_r.detach().cpu().numpy(), np.maximum(g["out"], 0)) < TOL
+
+
 @pytest.mark.parametrize("reorder", [None, "gorder", "rcm", "rabbit"])
 def test_fit_trains_and_reorder_is_consistent(golden_gcn, reorder):
     g = golden_gcn
