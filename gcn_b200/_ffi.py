@@ -17,7 +17,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libgcn_b200.so")
 
 F32, BF16 = 0, 1
 EPI_NONE, EPI_BIAS, EPI_RELU, EPI_ACCUM = 0, 1, 2, 4
-PLAN_DEFAULT, PLAN_ASSUME_SYMMETRIC, PLAN_NO_TRANSPOSE = 0, 1, 2
+PLAN_DEFAULT, PLAN_ASSUME_SYMMETRIC, PLAN_NO_TRANSPOSE, PLAN_PANEL, PLAN_NO_PANEL = 0, 1, 2, 4, 8
 ERR_NOGPU = -3
 
 

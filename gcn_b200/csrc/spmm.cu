@@ -4,6 +4,8 @@
 #include <string.h>
 
 #include <algorithm>
+#include <atomic>
+#include <thread>
 #include <vector>
 
 #include "common.h"
@@ -24,12 +26,21 @@ struct Matrix {  // one CSR resident in HBM + its block-class work lists
   int32_t* s_split_rows = nullptr;
   int32_t* s_split_ptr = nullptr;
   int64_t n_segs = 0, s_n_split = 0, s_n_partials = 0;
+  // panel class (high mean degree): items of 32-row panels + per-row block boundary table, see
+  // spmm_kernels.cuh spmm_panel_kernel
+  PanelItem* p_items = nullptr;
+  int32_t* p_subptr = nullptr;
+  int32_t* p_split_rows = nullptr;
+  int32_t* p_split_ptr = nullptr;
+  int64_t p_n_items = 0, p_n_split = 0, p_n_partials = 0, p_distinct = 0;
   int64_t n_items = 0, n_split = 0, n_partials = 0, n_long_rows = 0, max_row_nnz = 0;
   size_t bytes = 0;
 
   void release() {
     cudaFree(rowptr); cudaFree(cv); cudaFree(items); cudaFree(split_rows); cudaFree(split_ptr);
     cudaFree(segs); cudaFree(s_split_rows); cudaFree(s_split_ptr);
+    cudaFree(p_items); cudaFree(p_subptr); cudaFree(p_split_rows); cudaFree(p_split_ptr);
+    p_items = nullptr; p_subptr = nullptr; p_split_rows = nullptr; p_split_ptr = nullptr;
     s_split_rows = nullptr; s_split_ptr = nullptr;
     rowptr = nullptr; cv = nullptr; items = nullptr; split_rows = nullptr; split_ptr = nullptr;
     segs = nullptr;
@@ -61,8 +72,99 @@ static int64_t seg_target(int64_t nnz, int n_sm) {
   return std::max<int64_t>(64, std::min<int64_t>(kSegNnz, want));
 }
 
+
+// ---- panel class, plan time ------------------------------------------------------------------------
+// For every panel of kPanelRows consecutive rows: cut its columns (with multiplicity) into blocks of
+// ~tile_nnz non-zeros, record for every row where its non-zeros cross the cuts, cut heavy panels into
+// items of ~item_nnz non-zeros along the block list.  Host threads over panels.
+struct PanelBuild {
+  std::vector<PanelItem> items;
+  std::vector<int32_t> subptr, split_rows, split_ptr;
+  int64_t n_partials = 0, distinct = 0;
+};
+
+static void build_panels(const int32_t* rowptr, const int32_t* col, int64_t m, int64_t nnz, int tile_nnz,
+                         int item_nnz, PanelBuild* out) {
+  const int64_t n_panels = (m + kPanelRows - 1) / kPanelRows;
+  struct One { std::vector<int32_t> table; int32_t nb = 1; int64_t distinct = 0; };
+  std::vector<One> per(n_panels);
+  std::atomic<int64_t> next{0};
+  auto work = [&]() {
+    std::vector<int32_t> cols, cuts;
+    for (;;) {
+      const int64_t p = next.fetch_add(1);
+      if (p >= n_panels) break;
+      const int64_t r0 = p * kPanelRows, r1 = std::min<int64_t>(m, r0 + kPanelRows);
+      const int64_t zb = rowptr[r0], ze = rowptr[r1], P = ze - zb;
+      cols.assign(col + zb, col + ze);
+      std::sort(cols.begin(), cols.end());
+      int64_t distinct = P > 0 ? 1 : 0;
+      for (int64_t i = 1; i < P; ++i) distinct += cols[i] != cols[i - 1];
+      int64_t nb = std::max<int64_t>(1, std::min<int64_t>(32767, (P + tile_nnz - 1) / tile_nnz));
+      cuts.clear();
+      for (int64_t j = 1; j < nb; ++j) {
+        const int32_t c = cols[(size_t)(j * P / nb)];
+        if (cuts.empty() || c > cuts.back()) cuts.push_back(c);   // strictly increasing column cuts
+      }
+      nb = (int64_t)cuts.size() + 1;
+      One& o = per[p];
+      o.nb = (int32_t)nb;
+      o.distinct = distinct;
+      o.table.resize((size_t)kPanelRows * (nb + 1));
+      for (int r = 0; r < kPanelRows; ++r) {
+        int32_t* t = o.table.data() + (size_t)r * (nb + 1);
+        if (r0 + r >= m) {
+          for (int64_t j = 0; j <= nb; ++j) t[j] = (int32_t)ze;   // padding row: empty everywhere
+          continue;
+        }
+        const int32_t* cb = col + rowptr[r0 + r];
+        const int32_t* ce = col + rowptr[r0 + r + 1];
+        t[0] = rowptr[r0 + r];
+        const int32_t* pos = cb;
+        for (int64_t j = 1; j < nb; ++j) {
+          pos = std::lower_bound(pos, ce, cuts[(size_t)j - 1]);     // block j starts at the first column >= cut
+          t[j] = (int32_t)(rowptr[r0 + r] + (pos - cb));
+        }
+        t[nb] = rowptr[r0 + r + 1];
+      }
+    }
+  };
+  unsigned nt = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+  if (getenv("GCNB_HOST_THREADS")) nt = (unsigned)std::max(1, atoi(getenv("GCNB_HOST_THREADS")));
+  if (nnz < (1 << 20)) nt = 1;
+  std::vector<std::thread> th;
+  for (unsigned i = 1; i < nt; ++i) th.emplace_back(work);
+  work();
+  for (auto& t : th) t.join();
+
+  out->split_ptr.clear();
+  for (int64_t p = 0; p < n_panels; ++p) {
+    const One& o = per[p];
+    const int64_t r0 = p * kPanelRows, r1 = std::min<int64_t>(m, r0 + kPanelRows);
+    const int64_t P = (int64_t)rowptr[r1] - rowptr[r0];
+    const int32_t sub_off = (int32_t)out->subptr.size();
+    out->subptr.insert(out->subptr.end(), o.table.begin(), o.table.end());
+    out->distinct += o.distinct;
+    const int64_t n_items = std::max<int64_t>(1, std::min<int64_t>(o.nb, (P + item_nnz - 1) / item_nnz));
+    if (n_items == 1) {
+      out->items.push_back({(int32_t)r0, 0, o.nb, -1, 1, sub_off, o.nb, 0});
+    } else {
+      const int64_t base = out->n_partials;
+      for (int64_t i = 0; i < n_items; ++i)
+        out->items.push_back({(int32_t)r0, (int32_t)(i * o.nb / n_items), (int32_t)((i + 1) * o.nb / n_items),
+                              (int32_t)(base + i), (int32_t)n_items, sub_off, o.nb, 0});
+      for (int64_t r = r0; r < r1; ++r) {
+        out->split_rows.push_back((int32_t)r);
+        out->split_ptr.push_back((int32_t)(base + (r - r0) * n_items));
+      }
+      out->n_partials += (r1 - r0) * n_items;   // padding rows of the last panel write nothing
+    }
+  }
+  out->split_ptr.push_back((int32_t)out->n_partials);
+}
+
 static int upload_matrix(const int32_t* rowptr, const int32_t* col, const float* val, int64_t m,
-                         int64_t n, int64_t nnz, int n_sm, Matrix* M) {
+                         int64_t n, int64_t nnz, int n_sm, int flags, Matrix* M) {
   M->m = m; M->n = n; M->nnz = nnz;
   // block-class work lists (host, O(m))
   std::vector<WorkItem> items;
@@ -166,6 +268,38 @@ static int upload_matrix(const int32_t* rowptr, const int32_t* col, const float*
     GCNB_CHECK_CUDA(cudaMemcpy(M->s_split_ptr, s_split_ptr.data(), s_split_ptr.size() * 4,
                                cudaMemcpyHostToDevice));
     M->bytes += (s_split_rows.size() + s_split_ptr.size()) * 4;
+  }
+  // panel class: built when the mean row is long enough for rows of a panel to share columns, kept when
+  // the measured sharing (non-zeros per distinct column of a panel) says it pays.  GCNB_PANEL: -1 auto,
+  // 0 never, 1 always.
+  {
+    static const int panel_env = getenv("GCNB_PANEL") ? atoi(getenv("GCNB_PANEL")) : -1;
+    const int panel_mode = (flags & GCNB_PLAN_NO_PANEL) ? 0 : (flags & GCNB_PLAN_PANEL) ? 1 : panel_env;
+    static const int tile_nnz = getenv("GCNB_PANEL_TILE") ? atoi(getenv("GCNB_PANEL_TILE")) : 512;
+    static const int item_nnz = getenv("GCNB_PANEL_ITEM") ? atoi(getenv("GCNB_PANEL_ITEM")) : 32768;
+    static const double panel_min_share = getenv("GCNB_PANEL_MIN_SHARE") ? atof(getenv("GCNB_PANEL_MIN_SHARE")) : 1.25;
+    if (panel_mode != 0 && m > 0 && nnz > 0 && (panel_mode == 1 || nnz >= 96 * m)) {
+      PanelBuild pb;
+      build_panels(rowptr, col, m, nnz, std::max(32, tile_nnz), std::max(1024, item_nnz), &pb);
+      M->p_distinct = pb.distinct;
+      if (panel_mode == 1 || (double)nnz >= panel_min_share * (double)pb.distinct) {
+        M->p_n_items = (int64_t)pb.items.size();
+        M->p_n_split = (int64_t)pb.split_rows.size();
+        M->p_n_partials = pb.n_partials;
+        GCNB_CHECK_CUDA(cudaMalloc(&M->p_items, pb.items.size() * sizeof(PanelItem)));
+        GCNB_CHECK_CUDA(cudaMemcpy(M->p_items, pb.items.data(), pb.items.size() * sizeof(PanelItem), cudaMemcpyHostToDevice));
+        GCNB_CHECK_CUDA(cudaMalloc(&M->p_subptr, pb.subptr.size() * 4));
+        GCNB_CHECK_CUDA(cudaMemcpy(M->p_subptr, pb.subptr.data(), pb.subptr.size() * 4, cudaMemcpyHostToDevice));
+        M->bytes += pb.items.size() * sizeof(PanelItem) + pb.subptr.size() * 4;
+        if (!pb.split_rows.empty()) {
+          GCNB_CHECK_CUDA(cudaMalloc(&M->p_split_rows, pb.split_rows.size() * 4));
+          GCNB_CHECK_CUDA(cudaMalloc(&M->p_split_ptr, pb.split_ptr.size() * 4));
+          GCNB_CHECK_CUDA(cudaMemcpy(M->p_split_rows, pb.split_rows.data(), pb.split_rows.size() * 4, cudaMemcpyHostToDevice));
+          GCNB_CHECK_CUDA(cudaMemcpy(M->p_split_ptr, pb.split_ptr.data(), pb.split_ptr.size() * 4, cudaMemcpyHostToDevice));
+          M->bytes += (pb.split_rows.size() + pb.split_ptr.size()) * 4;
+        }
+      }
+    }
   }
   if (!items.empty()) {
     GCNB_CHECK_CUDA(cudaMalloc(&M->items, items.size() * sizeof(WorkItem)));
@@ -361,9 +495,33 @@ static int launch_packed(const LaunchArgs& a) {
   return GCNB_OK;
 }
 
+// panel class: one CTA per item, 32 warps = the 32 rows of the panel, column tiles of 32 vectors in grid.y
+template <typename TB, int VEC>
+static int launch_panel(const LaunchArgs& a) {
+  const Matrix& M = *a.M;
+  static const int l2pol = getenv("GCNB_L2POL") ? atoi(getenv("GCNB_L2POL")) : 1;
+  const int l2 = ((l2pol & 1) ? kL2Streams : 0) | ((l2pol & 2) ? kL2BLast : 0);
+  const unsigned ytiles = (unsigned)((a.k + 32 * VEC - 1) / (32 * VEC));
+  if (a.ldb * (int64_t)sizeof(TB) > 0xffffffffLL || ytiles > 65535)
+    return set_error(GCNB_ERR_UNSUPPORTED, "matrix too large for one grid");
+  spmm_panel_kernel<TB, VEC, 4><<<dim3((unsigned)M.p_n_items, ytiles), kPanelRows * 32, 0, a.stream>>>(
+      M.p_items, M.p_subptr, M.cv, (const TB*)a.B, (uint32_t)(a.ldb * sizeof(TB)), a.C, a.ldc, a.partials,
+      (int)M.m, a.k, a.bias, a.epi | l2);
+  GCNB_CHECK_CUDA(cudaGetLastError());
+  if (M.p_n_split > 0) {
+    spmm_reduce_kernel<<<(unsigned)M.p_n_split, 128, 0, a.stream>>>(
+        M.p_split_rows, M.p_split_ptr, a.partials, a.C, a.ldc, a.k, a.bias, a.epi);
+    GCNB_CHECK_CUDA(cudaGetLastError());
+  }
+  return GCNB_OK;
+}
+
 template <typename TB, int VEC, int NVMAX>
 static int launch_vec(const LaunchArgs& a) {
   const int nvec = (a.k + VEC - 1) / VEC;  // vectors per feature row
+  // wide feature rows on a matrix whose panels share columns: panel class (not in accumulate mode: the
+  // remote-column block of the partitioned SpMM has a handful of non-zeros per row)
+  if (a.M->p_n_items > 0 && nvec > 16 && !(a.epi & GCNB_EPI_ACCUM)) return launch_panel<TB, VEC>(a);
   // GCNB_PACKED = largest S the packed stream kernel may use (0: lane-group / block kernels instead)
   static const int packed = getenv("GCNB_PACKED") ? atoi(getenv("GCNB_PACKED")) : 8;
   // Measured (profiles/r01_v_*): products-shaped (50 nnz/row) k=32: 1.86 ms packed vs 2.87 ms lane-group
@@ -401,7 +559,7 @@ static int spmm_dispatch(const Matrix& M, const void* B, int b_dtype, int64_t ld
                          int64_t ldc, int k, const float* bias, int epi, cudaStream_t stream) {
   if (M.m == 0 || k == 0) return GCNB_OK;
   float* partials = nullptr;
-  const int64_t n_part = std::max(M.n_partials, M.s_n_partials);
+  const int64_t n_part = std::max(std::max(M.n_partials, M.s_n_partials), M.p_n_partials);
   if (n_part > 0)
     GCNB_CHECK_CUDA(cudaMallocAsync(&partials, (size_t)n_part * k * sizeof(float), stream));
   LaunchArgs a{&M, B, ldb, C, ldc, k, bias, epi, partials, stream};
@@ -489,7 +647,7 @@ int gcnb_plan_create(const int32_t* rowptr, const int32_t* col, const float* val
   if (!p) return set_error(GCNB_ERR_ALLOC, "out of host memory");
   p->device = device;
   p->n_sm = sm_count(device);
-  rc = upload_matrix(rowptr, col, val, m, n, nnz, p->n_sm, &p->a);
+  rc = upload_matrix(rowptr, col, val, m, n, nnz, p->n_sm, flags, &p->a);
   if (rc != GCNB_OK) { gcnb_plan_destroy(p); return rc; }
 
   if (flags & GCNB_PLAN_ASSUME_SYMMETRIC) {
@@ -504,7 +662,7 @@ int gcnb_plan_create(const int32_t* rowptr, const int32_t* col, const float* val
                       memcmp(t_val.data(), val, (size_t)nnz * 4) == 0))) {
       p->symmetric = true;  // bit-identical transpose: A^T·dY can run on A
     } else {
-      rc = upload_matrix(t_rowptr.data(), t_col.data(), t_val.data(), n, m, nnz, p->n_sm, &p->at);
+      rc = upload_matrix(t_rowptr.data(), t_col.data(), t_val.data(), n, m, nnz, p->n_sm, flags, &p->at);
       if (rc != GCNB_OK) { gcnb_plan_destroy(p); return rc; }
       p->has_t = true;
     }
@@ -534,6 +692,7 @@ int gcnb_plan_info(const gcnb_plan_t* plan, int64_t info[16]) {
   info[9] = (int64_t)(plan->a.bytes + plan->at.bytes + plan->stage_b_bytes + plan->stage_c_bytes);
   info[10] = plan->n_sm; info[11] = plan->a.n_split;
   info[12] = plan->a.n_segs; info[13] = plan->a.s_n_split;
+  info[14] = plan->a.p_n_items; info[15] = plan->a.p_distinct;
   return GCNB_OK;
 }
 

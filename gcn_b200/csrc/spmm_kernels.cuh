@@ -936,6 +936,197 @@ spmm_stream_packed_kernel(const Seg* __restrict__ segs, int n_segs, const int32_
   while (row < r1) flush();
 }
 
+// ---- panel class: 32 consecutive rows walk their columns in step, so that a gathered feature row is
+// ---- re-used by the other rows of the panel out of L1 ---------------------------------------------
+// The one idea the reference's tile format exists for (8-row column-ordered panels, tile.cu:11-103,
+// consumed per segment in flexspmm.cu:59-92): rows that are processed TOGETHER and reference the same
+// column should fetch that feature row from L2 once.  The stream kernel above cannot get that re-use: its
+// warps run through unrelated row segments at unrelated times, every non-zero is a 512-byte L2->SM
+// transfer, and on graphs with mean degree in the hundreds (Reddit-shaped) the 64 B/clk/SM L2 port is
+// the bound.  Here a CTA of 32 warps owns a PANEL of 32 consecutive rows, one row per warp, accumulators
+// in registers, no atomics.  At plan time (spmm.cu build_panels) the panel's column range is cut into
+// blocks of ~kPanelTileNnz non-zeros of the panel (a few hundred distinct 512-byte feature rows: an
+// L1-sized working set) and every row gets the offsets of its non-zeros at those cuts.  All 32 warps
+// process block t before any of them goes beyond block t+1 (two mbarriers, one block of drift allowed),
+// so a feature row gathered by one warp is an L1 hit for the other rows of the panel that reference it
+// inside the same block: nnz / distinct-columns-per-block L2 transfers are saved (1.8x on the
+// Reddit-shaped graph in degree order, 20x inside its hub rows).  Everything else is the stream kernel:
+// (col,val) slab, register ring of U gathers in flight, fma.rn.f32x2.
+// Heavy panels are cut along their block list into ITEMS of <= ~32 k non-zeros (one CTA each) whose
+// partial rows meet in spmm_reduce_kernel in fixed order: still no atomics, bit-reproducible.
+constexpr int kPanelRows = 32;
+
+struct PanelItem {
+  int32_t row0;      // first row of the panel
+  int32_t a, b;      // blocks [a, b) of the panel
+  int32_t slot;      // < 0: the item is the whole panel, rows go to C; else first partial row of the item
+  int32_t n_items;   // items of this panel (partial row of panel row r = slot + r * n_items)
+  int32_t sub_off;   // offset of the panel's boundary table in subptr
+  int32_t nb;        // blocks in the panel (the table has kPanelRows rows of nb + 1 offsets)
+  int32_t pad;
+};
+
+template <typename TB, int VEC, int U>
+__global__ void __launch_bounds__(kPanelRows * 32, 1)
+spmm_panel_kernel(const PanelItem* __restrict__ items, const int32_t* __restrict__ subptr,
+                  const int2* __restrict__ cv, const TB* __restrict__ B, uint32_t ldb_bytes,
+                  float* __restrict__ C, int64_t ldc, float* __restrict__ partials, int m, int k,
+                  const float* __restrict__ bias, int epi_l2) {
+  static_assert(32 % U == 0, "ring size must divide the slab");
+  __shared__ alignas(16) int2 s_cv[kPanelRows][32];
+  __shared__ alignas(8) uint64_t s_bar[2];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int epi_arg = epi_l2 & 0xff;
+  const uint64_t pol_s = l2_policy((epi_l2 & kL2Streams) ? 1 : 0);
+  const uint64_t pol_b = l2_policy((epi_l2 & kL2BLast) ? 2 : 0);
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(&s_bar[0])), "r"(kPanelRows));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(&s_bar[1])), "r"(kPanelRows));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  const uint32_t bar0 = (uint32_t)__cvta_generic_to_shared(&s_bar[0]);
+
+  const PanelItem it = items[blockIdx.x];
+  const int row = it.row0 + warp;
+  const int nblk = it.b - it.a;
+  const int32_t* bp = subptr + it.sub_off + (int64_t)warp * (it.nb + 1) + it.a;   // bp[t] = start of block a+t
+  const int z0 = __ldg(bp);
+  const int total = __ldg(bp + nblk) - z0;
+  const int coff = (blockIdx.y * 32 + lane) * VEC;
+  const bool cok = coff < k;
+  const char* bl = reinterpret_cast<const char*>(B + (cok ? coff : 0));
+
+  // ends of blocks tb .. tb+31 (stream positions), one per lane
+  int tb = 0, t = 0;
+  int bnd_c = __ldg(bp + min(1 + lane, nblk)) - z0;
+  int rend = __shfl_sync(0xffffffffu, bnd_c, 0);
+
+  float acc[VEC];
+#pragma unroll
+  for (int x = 0; x < VEC; ++x) acc[x] = 0.f;
+
+  auto boundary = [&]() {   // the stream position reached the end of block t (warp-uniform)
+    if (t == nblk - 1) {
+      if (row < m && cok) {
+        float* crow = it.slot < 0 ? C + (int64_t)row * ldc
+                                  : partials + ((int64_t)it.slot + (int64_t)warp * it.n_items) * k;
+        const int epi = it.slot < 0 ? epi_arg : 0;
+        float o[VEC];
+#pragma unroll
+        for (int x = 0; x < VEC; ++x) o[x] = epilogue(acc[x], bias, coff + x, epi);
+        store_vec<VEC>(crow + coff, o, pol_s);
+      }
+    } else {
+      // arrive on the barrier of block t; before starting block t+1 the whole panel must have finished
+      // block t-1 (one block of drift)
+      __syncwarp();
+      if (lane == 0)
+        asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar0 + 8u * (uint32_t)(t & 1)) : "memory");
+      if (t >= 1) {
+        const uint32_t bar = bar0 + 8u * (uint32_t)((t - 1) & 1), parity = (uint32_t)(((t - 1) >> 1) & 1);
+        uint32_t done = 0;
+        while (!done)
+          asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                       : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+      }
+    }
+    ++t;
+    int idx = t - tb;
+    if (idx == 32) {
+      tb = t;
+      bnd_c = __ldg(bp + min(1 + tb + lane, nblk)) - z0;
+      idx = 0;
+    }
+    rend = __shfl_sync(0xffffffffu, bnd_c, idx);
+  };
+
+  float av[U];
+  RawVec<TB, VEC> bv[U];
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    av[u] = 0.f;
+    bv[u].zero();
+  }
+  auto consume = [&](int u) {
+    float b[VEC];
+    bv[u].get(b);
+    if constexpr (VEC % 2 == 0) {
+#pragma unroll
+      for (int x = 0; x < VEC; x += 2) ffma2(acc[x], acc[x + 1], av[u], b[x], b[x + 1]);
+    } else {
+#pragma unroll
+      for (int x = 0; x < VEC; ++x) acc[x] = fmaf(av[u], b[x], acc[x]);
+    }
+  };
+
+  uint32_t slab_a, slab_l;
+  asm volatile("mov.u32 %0, %1;" : "=r"(slab_a) : "r"((uint32_t)__cvta_generic_to_shared(s_cv[warp])));
+  asm volatile("mov.u32 %0, %1;" : "=r"(slab_l) : "r"(slab_a + 8u * (uint32_t)lane));
+  const int2* src = cv + z0;
+  int2 e = make_int2(0, 0);
+  if (lane < total) e = ld_stream_int2(src + lane, pol_s);
+  auto refill = [&](int at) {
+    __syncwarp();
+    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(slab_l), "r"(e.x), "r"(e.y) : "memory");
+    __syncwarp();
+    if (at + 32 + lane < total) e = ld_stream_int2(src + at + 32 + lane, pol_s);
+  };
+  auto gather = [&](int u, int c, int vbits) {
+    av[u] = __int_as_float(vbits);
+    if (cok) bv[u].load(reinterpret_cast<const TB*>(bl + (uint64_t)(uint32_t)c * ldb_bytes), pol_b);
+  };
+  auto issue = [&](int u, int at) {
+    int2 q;
+    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(q.x), "=r"(q.y) : "r"(slab_a + 8u * (uint32_t)(at & 31)) : "memory");
+    gather(u, q.x, q.y);
+  };
+  auto issue2 = [&](int u, int at) {
+    int4 q;
+    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(q.x), "=r"(q.y), "=r"(q.z), "=r"(q.w)
+                 : "r"(slab_a + 8u * (uint32_t)(at & 31)) : "memory");
+    gather(u, q.x, q.y);
+    gather(u + 1, q.z, q.w);
+  };
+
+  if (total > 0) {
+    refill(0);
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (u < total) issue(u, u);
+  }
+  for (int g = 0; g < total; g += U) {
+    const int nxt = g + U;
+    if ((nxt & 31) == 0 && nxt < total) refill(nxt);
+    if (g + U <= rend && nxt + U <= total) {
+      if constexpr (U % 2 == 0) {
+#pragma unroll
+        for (int u = 0; u < U; u += 2) {
+          consume(u);
+          consume(u + 1);
+          issue2(u, nxt + u);
+        }
+      } else {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          consume(u);
+          issue(u, nxt + u);
+        }
+      }
+    } else {
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (g + u < total) {
+          while (g + u == rend) boundary();
+          consume(u);
+        }
+        if (nxt + u < total) issue(u, nxt + u);
+      }
+    }
+  }
+  while (t < nblk) boundary();   // the last block of the item and any trailing empty ones
+}
+
 // ---- block class -------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return (uint32_t)__cvta_generic_to_shared(p);

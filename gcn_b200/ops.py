@@ -56,7 +56,7 @@ class SpmmPlan:
     """
 
     def __init__(self, rowptr, col, val, shape, device=None, assume_symmetric=False,
-                 need_transpose=True):
+                 need_transpose=True, panel=None):
         rowptr = np.ascontiguousarray(rowptr, dtype=np.int32)
         col = np.ascontiguousarray(col, dtype=np.int32)
         val = np.ascontiguousarray(val, dtype=np.float32)
@@ -73,6 +73,8 @@ class SpmmPlan:
             flags |= _ffi.PLAN_ASSUME_SYMMETRIC
         elif not need_transpose:
             flags |= _ffi.PLAN_NO_TRANSPOSE
+        if panel is not None:   # None: the library decides (mean degree and measured column sharing)
+            flags |= _ffi.PLAN_PANEL if panel else _ffi.PLAN_NO_PANEL
         handle = ctypes.c_void_p()
         torch.cuda.init()
         _ffi.call("gcnb_plan_create", np_ptr(rowptr), np_ptr(col), np_ptr(val), m, n, len(col),
@@ -110,7 +112,7 @@ class SpmmPlan:
         _ffi.call("gcnb_plan_info", self._handle, buf)
         keys = ("m", "n", "nnz", "symmetric", "has_transpose", "rows_warp_class", "rows_block_class",
                 "block_items", "max_row_nnz", "device_bytes", "n_sm", "rows_split",
-                "stream_segments", "stream_rows_split")
+                "stream_segments", "stream_rows_split", "panel_items", "panel_distinct_columns")
         return {k: int(buf[i]) for i, k in enumerate(keys)}
 
     @property

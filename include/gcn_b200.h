@@ -49,6 +49,8 @@ extern "C" {
 #define GCNB_PLAN_DEFAULT 0
 #define GCNB_PLAN_ASSUME_SYMMETRIC 1 /* skip the check; A^T·dY runs on A (reference behaviour, gcn6.py:50-62) */
 #define GCNB_PLAN_NO_TRANSPOSE 2     /* never build A^T (forward-only plans) */
+#define GCNB_PLAN_PANEL 4            /* always build the panel class (32-row panels walking their columns in step) */
+#define GCNB_PLAN_NO_PANEL 8         /* never build it; default: built when nnz >= 96 m and the panels share columns */
 
 typedef struct gcnb_plan gcnb_plan_t;
 
@@ -74,7 +76,9 @@ int gcnb_plan_destroy(gcnb_plan_t* plan);
 /* info[0]=m [1]=n [2]=nnz [3]=symmetric(0/1) [4]=has_transpose [5]=rows in warp class
  * [6]=rows in block class [7]=block work items [8]=max row nnz [9]=device bytes held
  * [10]=SM count [11]=rows split across >1 block item [12]=stream-class segments
- * [13]=rows cut into several stream segments (they add one reduce launch) [14..15]=reserved (0) */
+ * [13]=rows cut into several stream segments (they add one reduce launch) [14]=panel-class work
+ * items (0: class not in use) [15]=distinct columns summed over the 32-row panels (nnz / this = how
+ * many rows of a panel share a gathered feature row on average; 0 when the panels were not built) */
 int gcnb_plan_info(const gcnb_plan_t* plan, int64_t info[16]);
 
 /* C[m x k] = A · B[n x k]  (+ bias[k]) (ReLU).   Replaces flexspmm() (flexspmm.cu:499-544) and

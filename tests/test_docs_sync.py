@@ -29,7 +29,7 @@ def test_every_profile_tag_is_indexed():
     tags = set()
     for cell in rows:
         tags |= {t.strip() for t in cell.split(",")}
-    seen = {m.group(1) for fn in os.listdir(os.path.join(ROOT, "profiles"))
-            if (m := re.match(r"r01_([a-z]+)_", fn))}
+    seen = {m.group(1) or m.group(2) for fn in os.listdir(os.path.join(ROOT, "profiles"))
+            if (m := re.match(r"(?:r01_([a-z]+)|(r02_[a-z]+))_", fn))}
     missing = sorted(seen - tags)
     assert not missing, f"profiles/ run tags without a line in profiles/README.md: {missing}"

@@ -253,11 +253,18 @@ def test_against_compiled_reference_kernel_on_gpu(golden_graph):
 
 
 # ---- full-size properties (BASELINE shapes; the oracle would take too long) ----------------------
-@pytest.mark.parametrize("shape,k", [("arxiv", 256), ("products", 100)])
+@pytest.mark.parametrize("shape,k", [("arxiv", 256), ("products", 100), ("reddit", 128), ("rmat", 64)])
 def test_full_size_properties(shape, k):
-    rp, ci, va, n = synth.make_graph(shape, device=DEV)
+    if shape == "rmat":     # R-MAT scale 22, edge factor 16: the sweep's shape at a size the test box generates fast
+        rp, ci, va, n = synth.make_graph("rmat", device=DEV, scale=22, edge_factor=16)
+    else:
+        rp, ci, va, n = synth.make_graph(shape, device=DEV)
+    if shape == "reddit":   # BASELINE config 3 names 114 M edges: the generator must realise them
+        assert abs(len(ci) - 114_832_965) <= 1000
     plan = ops.SpmmPlan(rp, ci, va, (n, n), device=DEV)
     assert plan.symmetric
+    if shape == "reddit":
+        assert plan.info()["panel_distinct_columns"] > 0    # mean degree 493: panels were built and measured
     g = torch.Generator(device=DEV).manual_seed(1)
     X = torch.randn(n, k, device=DEV, generator=g)
     Y = torch.randn(n, k, device=DEV, generator=g)
@@ -319,3 +326,72 @@ def test_packed_stream_kernel_narrow_widths(k):
     Bp.copy_(Bd)
     Cp = torch.empty(n, k + 8, device=DEV)[:, :k]
     assert rel_err(plan.spmm(Bp, out=Cp).cpu().numpy(), ref) < FP32_TOL
+
+
+# ---- panel class (32-row panels walking their columns in step; spmm_panel_kernel) -----------------
+def _hub_graph(n, e, seed):
+    """Skewed rows AND columns: the first panels are nearly dense (they get cut into several items whose
+    partial rows meet in the fixed-order reduce), the tail rows hold a few non-zeros."""
+    import scipy.sparse as sp
+    rng = np.random.default_rng(seed)
+    r = (n * rng.random(e) ** 3).astype(np.int64)
+    c = (n * rng.random(e) ** 2).astype(np.int64)
+    a = sp.coo_matrix((np.ones(e), (r, c)), shape=(n, n)).tocsr()
+    a = ((a + a.T) > 0).astype(np.float64)
+    a.setdiag(0)
+    a.eliminate_zeros()
+    return graph.normalize_adj(a)
+
+
+@pytest.mark.parametrize("n,e", [(4001, 1_500_000), (700, 6000), (2500, 300_000)])
+@pytest.mark.parametrize("k", [68, 100, 128, 200, 602])
+def test_panel_class_matches_oracle(n, e, k):
+    A = _hub_graph(n, e, k + n)
+    rng = np.random.default_rng(k)
+    B = rng.standard_normal((n, k)).astype(np.float32)
+    plan = ops.SpmmPlan.from_scipy(A, device=DEV, panel=True)
+    info = plan.info()
+    assert info["panel_items"] >= (n + 31) // 32 and info["panel_distinct_columns"] > 0
+    Bd = torch.from_numpy(B).to(DEV)
+    C = plan.spmm(Bd)
+    ref = SO.spmm_f64(A.indptr, A.indices, A.data, n, B)
+    assert rel_err(C.cpu().numpy(), ref) < FP32_TOL
+    # no atomics anywhere: bit-reproducible, also against a second plan
+    assert torch.equal(C, plan.spmm(Bd))
+    assert torch.equal(C, ops.SpmmPlan.from_scipy(A, device=DEV, panel=True).spmm(Bd))
+    # the stream class on the same matrix agrees to rounding
+    C2 = ops.SpmmPlan.from_scipy(A, device=DEV, panel=False).spmm(Bd)
+    assert rel_err(C2.cpu().numpy(), ref) < FP32_TOL
+    # epilogue flags and transposed product (symmetric: same plan)
+    bias = torch.from_numpy(rng.standard_normal(k).astype(np.float32)).to(DEV)
+    Cb = plan.spmm(Bd, bias=bias, relu=True).cpu().numpy()
+    assert rel_err(Cb, np.maximum(ref + bias.cpu().numpy(), 0)) < FP32_TOL
+    assert rel_err(plan.spmm_t(Bd).cpu().numpy(), SO.spmm_t_f64(A.indptr, A.indices, A.data, n, B)) < FP32_TOL
+
+
+def test_panel_class_items_are_cut_and_reduced():
+    """The dense head of _hub_graph(4001, 1.5 M) exceeds 32 k non-zeros per panel: several items per panel."""
+    A = _hub_graph(4001, 1_500_000, 5)
+    assert int(A.indptr[32]) > 2 * 32768
+    plan = ops.SpmmPlan.from_scipy(A, device=DEV, panel=True)
+    assert plan.info()["panel_items"] > (4001 + 31) // 32
+
+
+@pytest.mark.parametrize("k", [100, 256])
+def test_panel_class_bf16_and_strides(k):
+    A = _hub_graph(2500, 300_000, 9)
+    n = A.shape[0]
+    rng = np.random.default_rng(3)
+    B = rng.standard_normal((n, k)).astype(np.float32)
+    plan = ops.SpmmPlan.from_scipy(A, device=DEV, panel=True)
+    Bb = torch.from_numpy(B).to(DEV).to(torch.bfloat16)
+    ref = SO.spmm_f64(A.indptr, A.indices, A.data, n, Bb.float().cpu().numpy())
+    assert rel_err(plan.spmm(Bb).cpu().numpy(), ref) < 1e-5      # exact bf16 inputs, fp32 accumulation
+    assert rel_err(plan.spmm(Bb).cpu().numpy(), SO.spmm_f64(A.indptr, A.indices, A.data, n, B)) < BF16_TOL
+    # padded pitch of B and of C
+    Bp = torch.zeros(n, k + 12, device=DEV)
+    Bp[:, :k] = torch.from_numpy(B).to(DEV)
+    out = torch.full((n, k + 8), 7.0, device=DEV)
+    plan.spmm(Bp[:, :k], out=out[:, :k])
+    assert rel_err(out[:, :k].cpu().numpy(), SO.spmm_f64(A.indptr, A.indices, A.data, n, B)) < FP32_TOL
+    assert torch.all(out[:, k:] == 7.0)
