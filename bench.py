@@ -89,6 +89,9 @@ def parse():
                     help="N=1 spmm mode: other GPU implementations timed on the same inputs (bench leg only): "
                          "fast = cuSPARSE CSR ALG3 + torch.spmm CUDA; all = + the reference's flexspmm.so on its tiles")
     ap.add_argument("--no-epoch", action="store_true", help="spmm mode: skip the `epoch` object of the line")
+    ap.add_argument("--k-sweep", default="",
+                    help="N=1 spmm mode: comma-separated feature widths timed on ONE generated graph / plan (the R-MAT "
+                         "sweep of BASELINE config 5); prints one short JSON line per width instead of the bench line")
     ap.add_argument("--no-parity", action="store_true", help="N>1: skip the untimed parity_check")
     return ap.parse_args()
 
@@ -517,6 +520,32 @@ def run_single(args):
     plan_s = time.perf_counter() - t0
     info = plan.info()
     dt = torch.float32 if args.dtype == "f32" else torch.bfloat16
+    if args.k_sweep:
+        peak, _ = peaks()
+        with ClockSampler(0) as clk:
+            for kk in [int(x) for x in args.k_sweep.split(",") if x]:
+                g = torch.Generator(device=device).manual_seed(15)
+                B = torch.randn(n, kk, device=device, generator=g).to(dt)
+                C = torch.empty(n, kk, device=device, dtype=torch.float32)
+                ms_avg, ms_med, ms_min = time_steps(lambda: plan.spmm(B, out=C), args.steps, args.warmup, device)
+                abytes, flops = synth.spmm_bytes_flops(n, n, nnz, kk, b_bytes=4 if args.dtype == "f32" else 2)
+                # linearity + checksum-of-checksums self-check at full size (untimed)
+                colsum = torch.from_numpy(np.bincount(ci, weights=va.astype(np.float64), minlength=n)).to(device)
+                lhs = C.double().sum(0)
+                rhs = colsum @ B.double()
+                chk = float((lhs - rhs).abs().max() / rhs.abs().max().clamp_min(1e-30))
+                print(json.dumps({"metric": METRIC, "value": flops / (ms_avg * 1e-3) / 1e9, "unit": UNIT, "n_gpus": 1,
+                                  "ms_per_step": ms_avg, "ms_median": ms_med, "ms_min": ms_min, "steps": args.steps,
+                                  "dtype": args.dtype,
+                                  "config": {"workload": workload_string(name, kk), "n": n, "nnz": nnz, "k": kk,
+                                             "max_row_nnz": info["max_row_nnz"], "plan_build_s": round(plan_s, 2)},
+                                  "roofline": {"bound": "hbm", "achieved": abytes / (ms_avg * 1e-3) / 1e9, "peak": peak,
+                                               "unit": "GB/s", "frac": abytes / (ms_avg * 1e-3) / 1e9 / peak,
+                                               "algorithmic_bytes_per_launch": abytes},
+                                  "checksum_rel_err": chk}), flush=True)
+                del B, C
+                torch.cuda.empty_cache()
+        return
     g = torch.Generator(device=device).manual_seed(15)
     pitch = max(args.pitch, k)
     B = torch.randn(n, pitch, device=device, generator=g).to(dt)[:, :k]

@@ -16,7 +16,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libgcn_b200.so")
 
 F32, BF16 = 0, 1
-EPI_NONE, EPI_BIAS, EPI_RELU, EPI_ACCUM = 0, 1, 2, 4
+EPI_NONE, EPI_BIAS, EPI_RELU, EPI_ACCUM, EPI_DROPOUT, EPI_MASK = 0, 1, 2, 4, 8, 16
 PLAN_DEFAULT, PLAN_ASSUME_SYMMETRIC, PLAN_NO_TRANSPOSE, PLAN_PANEL, PLAN_NO_PANEL = 0, 1, 2, 4, 8
 ERR_NOGPU = -3
 
@@ -54,6 +54,14 @@ SIGNATURES = {
     "gcnb_permute_rows": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     "gcnb_xw": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_int64, c_int, c_void_p, c_int64,
                         c_int64, c_int, c_int, c_void_p, c_int, c_int, c_void_p]),
+    "gcnb_xw_ex": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_int64, c_int, c_void_p, c_int64,
+                           c_int64, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p, c_int64, ctypes.c_float,
+                           ctypes.c_uint32, c_int, c_void_p]),
+    "gcnb_dropout_keeps": (c_int, [c_int64, c_int, c_int, ctypes.c_float, ctypes.c_uint32]),
+    "gcnb_logsoftmax_nll_fwd": (c_int, [c_void_p, c_int64, c_int64, c_int, c_void_p, c_void_p, c_int64, c_int64,
+                                        c_void_p, c_int64, c_void_p, c_void_p]),
+    "gcnb_logsoftmax_nll_bwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int,
+                                        c_int, c_void_p, c_int64, c_void_p]),
     "gcnb_peer_alloc": (c_int, [c_int, c_int64, POINTER(c_void_p), c_void_p]),
     "gcnb_peer_free": (c_int, [c_int, c_void_p]),
     "gcnb_peer_open": (c_int, [c_int, c_void_p, POINTER(c_void_p)]),

@@ -380,6 +380,10 @@ static int launch_stream(const LaunchArgs& a, int64_t gs, unsigned ytiles) {
       case 3: launch_stream_cfg<TB, VEC, NV, 8, 8>(a, gs, ytiles); break;
       case 4: launch_stream_cfg<TB, VEC, NV, 2, 12>(a, gs, ytiles); break;
       case 5: launch_stream_cfg<TB, VEC, NV, 8, 6>(a, gs, ytiles); break;
+      case 6: launch_stream_cfg<TB, VEC, NV, 3, 10>(a, gs, ytiles); break;   // 48 regs, 40 warps/SM, 3 in flight each
+      case 7: launch_stream_cfg<TB, VEC, NV, 3, 12>(a, gs, ytiles); break;   // 40 regs, 48 warps/SM
+      case 8: launch_stream_cfg<TB, VEC, NV, 3, 8>(a, gs, ytiles); break;
+      case 9: launch_stream_cfg<TB, VEC, NV, 2, 16>(a, gs, ytiles); break;   // 32 regs, 64 warps/SM
       default:
         if constexpr (R <= 2) launch_stream_cfg<TB, VEC, NV, 4, 10>(a, gs, ytiles);
         else launch_stream_cfg<TB, VEC, NV, 4, 8>(a, gs, ytiles);
@@ -540,8 +544,18 @@ static int launch_vec(const LaunchArgs& a) {
   if (nvec <= 8 && stream_min >= 8) return launch_one<TB, VEC, 8, 1>(a);
   if (nvec <= 16 && stream_min >= 16) return launch_one<TB, VEC, 16, 1>(a);
   if (nvec <= 32) return launch_one<TB, VEC, 32, 1>(a);
-  // wide rows: whole warp per row, NV vectors per lane, as few column tiles as possible
-  const int tiles = (nvec + 32 * NVMAX - 1) / (32 * NVMAX);
+  // wide rows: whole warp per row, NV vectors per lane, as few column tiles as possible — unless the
+  // gathered operand is re-used heavily (mean row >= 64 non-zeros) and does not fit L2 while a 32-vector
+  // column slice of it does: then one slice per grid.y (they run one after the other) keeps the slice
+  // L2-resident.  Measured on the Reddit-shaped graph at k = 602 (profiles/r02_d_ncu_reddit_deg_k602.txt):
+  // 71 GB of DRAM reads in 19.3 ms with two 384-column slices.  GCNB_WIDE_NV caps NV (0 = this rule).
+  static const int wide_nv = getenv("GCNB_WIDE_NV") ? atoi(getenv("GCNB_WIDE_NV")) : 0;
+  int nvmax = NVMAX;
+  if (wide_nv > 0) nvmax = std::min(NVMAX, wide_nv);
+  else if (a.M->nnz >= 64 * a.M->m && (double)a.M->n * a.k * sizeof(TB) > 100e6 &&
+           (double)a.M->n * 32 * VEC * sizeof(TB) <= 130e6)
+    nvmax = 1;
+  const int tiles = (nvec + 32 * nvmax - 1) / (32 * nvmax);
   const int nv = (nvec + 32 * tiles - 1) / (32 * tiles);
   if (nv <= 1) return launch_one<TB, VEC, 32, 1>(a);
   if (nv == 2) return launch_one<TB, VEC, 32, 2>(a);

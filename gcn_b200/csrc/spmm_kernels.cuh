@@ -593,13 +593,15 @@ spmm_stream_kernel(const Seg* __restrict__ segs, int n_segs, const int32_t* __re
                    const int2* __restrict__ cv, const TB* __restrict__ B, uint32_t ldb_bytes,
                    float* __restrict__ C, int64_t ldc, float* __restrict__ partials, int k,
                    const float* __restrict__ bias, int epi_l2) {
-  static_assert(32 % U == 0, "ring size must divide the slab");
+  // ring depths that divide 32 never straddle a 32-entry slab; others (U = 3: the measured per-warp cap on
+  // gathers in flight) use a circular slab of two 32-entry halves
+  constexpr int SL = (32 % U == 0) ? 32 : 64;
   // bits 8.. of the last argument: L2 eviction priorities (kL2Streams: (col,val) stream and C rows are
   // evict_first; kL2BLast: gathered feature rows are evict_last), chosen by the host (spmm.cu)
   const int epi_arg = epi_l2 & 0xff;
   const uint64_t pol_s = l2_policy((epi_l2 & kL2Streams) ? 1 : 0);
   const uint64_t pol_b = l2_policy((epi_l2 & kL2BLast) ? 2 : 0);
-  __shared__ alignas(16) int2 s_cv[kStreamWarps][32];
+  __shared__ alignas(16) int2 s_cv[kStreamWarps][SL];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int s = blockIdx.x * kStreamWarps + warp;
   if (s >= n_segs) return;   // warp-uniform; no block-wide barrier below
@@ -714,9 +716,9 @@ spmm_stream_kernel(const Seg* __restrict__ segs, int n_segs, const int32_t* __re
   // nxt crosses a multiple of 32 (every earlier entry of the old slab has been issued by then)
   int2 e = make_int2(0, 0);
   if (lane < total) e = ld_stream_int2(src + lane, pol_s);
-  auto refill = [&](int at) {   // make slab hold stream positions [at, at+32)
+  auto refill = [&](int at) {   // make slab hold stream positions [at, at+32) (at: multiple of 32)
     __syncwarp();
-    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(slab_l), "r"(e.x), "r"(e.y) : "memory");
+    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(slab_l + 8u * (uint32_t)(at & (SL - 32))), "r"(e.x), "r"(e.y) : "memory");
     __syncwarp();
     if (at + 32 + lane < total) e = ld_stream_int2(src + at + 32 + lane, pol_s);
   };
@@ -729,7 +731,7 @@ spmm_stream_kernel(const Seg* __restrict__ segs, int n_segs, const int32_t* __re
   };
   auto issue = [&](int u, int at) {   // gather non-zero `at` (valid) into ring slot u
     int2 q;
-    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(q.x), "=r"(q.y) : "r"(slab_a + 8u * (uint32_t)(at & 31)) : "memory");
+    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(q.x), "=r"(q.y) : "r"(slab_a + 8u * (uint32_t)(at & (SL - 1))) : "memory");
     gather(u, q.x, q.y);
   };
   auto issue2 = [&](int u, int at) {   // two consecutive non-zeros (at even) with one LDS.128 broadcast
@@ -748,7 +750,13 @@ spmm_stream_kernel(const Seg* __restrict__ segs, int n_segs, const int32_t* __re
 
   for (int g = 0; g < total; g += U) {   // consume [g, g+U), issue [g+U, g+2U)
     const int nxt = g + U;
-    if ((nxt & 31) == 0 && nxt < total) refill(nxt);
+    if constexpr (SL == 32) {
+      if ((nxt & 31) == 0 && nxt < total) refill(nxt);
+    } else {
+      // the group issued in this turn is [nxt, nxt+U): store its 32-entry chunk when it starts one
+      const int last = nxt + U - 1;
+      if ((last >> 5) != ((nxt - 1) >> 5) && (last & ~31) < total) refill(last & ~31);
+    }
     if (g + U <= rend && nxt + U <= total) {
       // fast path: no row end inside the group, the next group is complete
       if constexpr (U % 2 == 0) {

@@ -1,0 +1,517 @@
+// Dense feature transform for the layer shapes of the GCN epoch — D[M x N] = X[M x K] · op(W) (+bias)(ReLU)
+// (dropout)(mask) with M = vertices (millions), K and N = feature widths (<= a few hundred) — as a
+// persistent, warp-specialised tcgen05 kernel.  Replaces torch.mm(input, self.weight) of the reference
+// layer (pygcn/gcn6.py:131, :191; gcn5.py:88, :136), the F.dropout that follows it (gcn6.py:246) and, in
+// the backward pass, the dropout / ReLU masking of dH = dS·W^T (autograd of gcn6.py:245-246).
+//
+// Why a second kernel next to xw_tcgen05.cu: that one (one 4-warp CTA per 128 x BN tile, k-blocks of 16,
+// every fp32 value converted to tf32 hi/lo by the same threads that wait for it, a CTA-wide barrier per
+// k-block, per-thread row stores) ran at ~27 % of the HBM time of these shapes.
+// Here one CTA per SM loops over its 128-row tiles, with fixed warp roles and separate rings per stream:
+//   warp 0      X producer: one TMA tensor-map load per k-chunk (128 rows x 32 floats, SWIZZLE_128B, rows
+//               past M and columns past K zero-filled by the TMA unit) into a DEEP ring — the X chunks are
+//               the only HBM reads of the kernel, and ~100 KB of them must be in flight per SM to cover
+//               the HBM latency (the first version of this kernel staged X, lo(X) and W together, had
+//               32-64 KB of X in flight and ran at 16 B/clk/SM, profiles/r02_d_launches_epoch_products.csv)
+//   warp 2      W producer: bulk copies of the prepared W chunk (hi | lo images, L2-resident) into a ring of 2
+//   warp 1      MMA issuer (one elected thread): tcgen05.mma kind::tf32, A and B from shared memory,
+//               accumulator in TMEM, two accumulator buffers so the epilogue of tile i overlaps the MMAs of
+//               tile i+1; tcgen05.commit frees the rings / publishes the accumulator
+//   warps 4-7   converters: only the LOW part of the 3xTF32 split is computed, lo = tf32(x - trunc13(x)),
+//               into a ring of 2; the HIGH part is the raw fp32 word with its 13 low mantissa bits cleared
+//   warps 8-15  epilogue (8-11 when BN = 64): tcgen05.ld, bias / ReLU / dropout / mask with thread = row,
+//               one 32-bit word of mask bits per 32 outputs, then a transpose through a private
+//               shared-memory tile so that every store instruction writes full 128-byte lines
+//   * x·w = hi_x·hi_w + hi_x·lo_w + lo_x·hi_w (three MMAs per k-step of 8), error ~1e-6 of fp32 like the
+//     first kernel (W is split with round-to-nearest by the prep kernel; |lo_x·lo_w| <= 2^-21 |x·w|).
+//   * fused epilogues (GCNB_EPI_*): bias, ReLU, DROPOUT (keep bits from a counter hash of (seed, group of 4
+//     elements), p quantised to 1/256; out = keep ? out / (1-p) : 0), optional output of the bit mask
+//     [out > 0] (1 bit per element), MASK (out = bit ? out / (1-p) : 0 — the backward of ReLU followed by
+//     dropout costs 1/32 of a word per element instead of re-reading the forward activation).
+// Used by gcnb_xw / gcnb_xw_ex when X is not transposed, 16-byte aligned with ldx % 4 == 0, M >= 1024 and
+// K <= 4096, precision 0 or 1; everything else stays on xw_tcgen05.cu.
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdlib.h>
+
+#include <algorithm>
+#include <atomic>
+
+#include "common.h"
+
+namespace gcnb {
+namespace xs {
+
+constexpr int BM = 128;          // rows per tile == UMMA M
+constexpr int KC = 32;           // floats per k-chunk: one 128-byte swizzle row
+constexpr int CHUNK_A = BM * 128;                 // bytes of one A chunk (raw or lo)
+constexpr int STG_PITCH = 144;   // bytes per row of the epilogue's transpose tile (32 floats + 16 pad)
+constexpr int STG_BYTES = 32 * STG_PITCH;
+constexpr int SMEM_MAX = 232448; // 227 KB of dynamic shared memory per CTA
+
+__host__ __device__ constexpr int epi_warps(int bn) { return bn <= 64 ? 4 : 8; }
+__host__ __device__ constexpr int threads_for(int bn) { return (8 + epi_warps(bn)) * 32; }
+__host__ __device__ constexpr int w_chunk(int bn) { return 2 * bn * 128; }      // hi | lo
+__host__ __device__ constexpr int fixed_bytes(int bn) {
+  return 2 * w_chunk(bn) + 2 * CHUNK_A + epi_warps(bn) * STG_BYTES + 1024 /* barriers */ + 1024 /* alignment */;
+}
+__host__ __device__ constexpr int ring_a(int bn) { return (SMEM_MAX - fixed_bytes(bn)) / CHUNK_A; }
+__host__ __device__ constexpr int smem_bytes(int bn) { return fixed_bytes(bn) + ring_a(bn) * CHUNK_A; }
+
+struct Params {
+  const uint8_t* w_img;      // [ntiles][nkc] { hi[bn x 128 B] | lo[bn x 128 B] }, swizzled like the A chunk
+  float* D; int64_t ldd;
+  const uint32_t* mask_in;   // GCNB_EPI_MASK: bit (row, col) = word[row * ldm + col / 32] >> (col % 32)
+  uint32_t* mask_out;        // optional: bit = (out > 0) after the epilogue
+  int64_t ldm;               // words per row of the bit masks
+  const float* bias;
+  int64_t M; int N; int K;
+  int nkc, ntiles;
+  int64_t mtiles;
+  int epi;
+  float scale;               // 1/(1-p) for DROPOUT and MASK (p quantised to 1/256)
+  uint32_t keep_thresh;      // DROPOUT: keep when the element's hash byte >= thresh (0..255)
+  uint32_t seed;
+  int d_vec;                 // 16-byte stores of D allowed
+};
+
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  while (!done) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+  }
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+// shared-memory matrix descriptor: K-major, SWIZZLE_128B (layout type 2), 8-row groups 1024 bytes apart
+__device__ __forceinline__ uint64_t make_desc_sw128(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3fff);
+  d |= (uint64_t)1 << 16;                       // leading byte offset: unused for swizzled K-major
+  d |= (uint64_t)(1024 >> 4) << 32;             // stride byte offset
+  d |= (uint64_t)1 << 46;                       // descriptor version (Blackwell)
+  d |= (uint64_t)2 << 61;                       // SWIZZLE_128B
+  return d;
+}
+// instruction descriptor: D fp32, A/B TF32, both K-major, M = 128, N = n
+__host__ __device__ constexpr uint32_t make_idesc(int n) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+}
+__device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ uint32_t to_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return r;
+}
+// counter hash for the dropout keep bits: one 32-bit word per group of 4 consecutive columns of a row
+// (group index = row * ceil(N/4) + col/4), one byte per element
+__host__ __device__ __forceinline__ uint32_t mix32(uint64_t idx, uint32_t seed) {
+  uint32_t x = (uint32_t)idx ^ seed, y = (uint32_t)(idx >> 32) + 0x9e3779b9u * (seed | 1u);
+  x *= 0x85ebca6bu; x ^= x >> 13; x += y; x *= 0xc2b2ae35u; x ^= x >> 16; x *= 0x27d4eb2fu; x ^= x >> 15;
+  return x;
+}
+__host__ __device__ __forceinline__ uint32_t drop_thresh(float p) {   // p quantised to 1/256, < 1
+  int t = (int)(p * 256.f + 0.5f);
+  return (uint32_t)(t < 0 ? 0 : (t > 255 ? 255 : t));
+}
+
+}  // namespace xs
+}  // namespace gcnb
+
+namespace gcnb {
+namespace xs {
+
+template <int BN, int MODE>   // MODE 0: 3xTF32 (fp32 parity), 1: single-pass TF32
+__global__ void __launch_bounds__(threads_for(BN), 1)
+xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  constexpr int RA = ring_a(BN);                  // X chunks in flight
+  constexpr int NE = epi_warps(BN);               // epilogue warps
+  constexpr int NEG = NE / 4;                     // epilogue warps per TMEM lane quadrant
+  constexpr int W_CHUNK = w_chunk(BN);
+  constexpr uint32_t W_BYTES = (MODE == 0 ? 2 : 1) * BN * 128;
+  constexpr uint32_t IDESC = make_idesc(BN);
+  constexpr int TMEM_COLS = 2 * BN;               // two accumulator buffers (128 / 256 columns)
+  static_assert(RA >= 2, "no room for the X ring");
+  // 1024-byte alignment (of the shared-space address) for the 128-byte swizzle atoms
+  uint8_t* smem = smem_raw + ((1024u - (smem_addr(smem_raw) & 1023u)) & 1023u);
+  uint8_t* ring = smem;                            // RA x 16 KB raw X chunks
+  uint8_t* lo = ring + RA * CHUNK_A;               // 2 x 16 KB low parts
+  uint8_t* wbuf = lo + 2 * CHUNK_A;                // 2 x W chunk
+  uint8_t* stg = wbuf + 2 * W_CHUNK;               // NE transpose tiles
+  uint64_t* bars = reinterpret_cast<uint64_t*>(stg + NE * STG_BYTES);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * RA + 12);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t bar0 = smem_addr(bars);
+  auto FULLA = [&](int s) { return bar0 + 8u * (uint32_t)s; };
+  auto EMPTYA = [&](int s) { return bar0 + 8u * (uint32_t)(RA + s); };
+  auto FULLW = [&](int s) { return bar0 + 8u * (uint32_t)(2 * RA + s); };
+  auto EMPTYW = [&](int s) { return bar0 + 8u * (uint32_t)(2 * RA + 2 + s); };
+  auto CONV = [&](int s) { return bar0 + 8u * (uint32_t)(2 * RA + 4 + s); };
+  auto LOEMPTY = [&](int s) { return bar0 + 8u * (uint32_t)(2 * RA + 6 + s); };
+  auto TFULL = [&](int b) { return bar0 + 8u * (uint32_t)(2 * RA + 8 + b); };
+  auto TEMPTY = [&](int b) { return bar0 + 8u * (uint32_t)(2 * RA + 10 + b); };
+
+  if (tid == 0) {
+    for (int s = 0; s < RA; ++s) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(FULLA(s)));
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(EMPTYA(s)));
+    }
+    for (int b = 0; b < 2; ++b) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(FULLW(b)));
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(EMPTYW(b)));
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 128;" ::"r"(CONV(b)));
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(LOEMPTY(b)));
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(TFULL(b)));
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(TEMPTY(b)), "r"(NE * 32));
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                 ::"r"(smem_addr(tmem_slot)), "r"(TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int64_t n_tiles = p.mtiles * p.ntiles;     // n-tile fastest: the CTAs sharing an X tile run together
+
+  if (warp == 0) {
+    // ---------------- X producer ----------------
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        const int64_t m0 = (t / p.ntiles) * BM;
+        for (int kc = 0; kc < p.nkc; ++kc, ++it) {
+          const int s = it % RA;
+          mbar_wait(EMPTYA(s), ((it / RA) & 1) ^ 1);
+          const uint32_t full = FULLA(s);
+          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(full), "r"((uint32_t)CHUNK_A) : "memory");
+          asm volatile(
+              "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+              ::"r"(smem_addr(ring + s * CHUNK_A)), "l"(&tmap_x), "r"(kc * KC), "r"((int)m0), "r"(full) : "memory");
+        }
+      }
+    }
+  } else if (warp == 2) {
+    // ---------------- W producer ----------------
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        const int nt = (int)(t % p.ntiles);
+        for (int kc = 0; kc < p.nkc; ++kc, ++it) {
+          const int s = it & 1;
+          mbar_wait(EMPTYW(s), ((it >> 1) & 1) ^ 1);
+          const uint32_t full = FULLW(s);
+          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(full), "r"(W_BYTES) : "memory");
+          const uint8_t* src_w = p.w_img + ((int64_t)nt * p.nkc + kc) * W_CHUNK;
+          asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                       ::"r"(smem_addr(wbuf + s * W_CHUNK)), "l"(src_w), "r"(W_BYTES), "r"(full) : "memory");
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ---------------- MMA issuer ----------------
+    if (lane == 0) {
+      uint32_t it = 0, tl = 0;
+      for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++tl) {
+        const uint32_t buf = tl & 1;
+        mbar_wait(TEMPTY(buf), ((tl >> 1) & 1) ^ 1);       // the epilogue has drained this accumulator
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t tmem_d = tmem_base + buf * BN;
+        for (int kc = 0; kc < p.nkc; ++kc, ++it) {
+          const int sa = it % RA, sw = it & 1;
+          mbar_wait(FULLA(sa), (it / RA) & 1);
+          mbar_wait(FULLW(sw), (it >> 1) & 1);
+          if constexpr (MODE == 0) mbar_wait(CONV(sw), (it >> 1) & 1);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t a_raw = smem_addr(ring + sa * CHUNK_A), a_lo = smem_addr(lo + sw * CHUNK_A);
+          const uint32_t w_hi = smem_addr(wbuf + sw * W_CHUNK), w_lo = w_hi + BN * 128;
+#pragma unroll
+          for (int ks = 0; ks < KC / 8; ++ks) {     // K = 8 tf32 = 32 bytes per MMA: advance inside the swizzle row
+            const uint32_t o = ks * 32;
+            const uint32_t acc = (kc > 0 || ks > 0) ? 1u : 0u;
+            mma_tf32(tmem_d, make_desc_sw128(a_raw + o), make_desc_sw128(w_hi + o), IDESC, acc);
+            if constexpr (MODE == 0) {
+              mma_tf32(tmem_d, make_desc_sw128(a_raw + o), make_desc_sw128(w_lo + o), IDESC, 1u);
+              mma_tf32(tmem_d, make_desc_sw128(a_lo + o), make_desc_sw128(w_hi + o), IDESC, 1u);
+            }
+          }
+          commit(EMPTYA(sa));                        // ring slots reusable once these MMAs have read them
+          commit(EMPTYW(sw));
+          if constexpr (MODE == 0) commit(LOEMPTY(sw));
+        }
+        commit(TFULL(buf));                          // accumulator complete
+      }
+    }
+  } else if (warp >= 4 && warp < 8) {
+    // ---------------- converters: lo = tf32(x - trunc13(x)) on the physical (swizzled) layout ----------------
+    if constexpr (MODE == 0) {
+      const int ct = tid - 128;                      // 0..127
+      uint32_t it = 0;
+      for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        for (int kc = 0; kc < p.nkc; ++kc, ++it) {
+          const int sa = it % RA, sw = it & 1;
+          mbar_wait(FULLA(sa), (it / RA) & 1);
+          mbar_wait(LOEMPTY(sw), ((it >> 1) & 1) ^ 1);
+          uint8_t* raw = ring + sa * CHUNK_A;
+          uint8_t* lop = lo + sw * CHUNK_A;
+#pragma unroll
+          for (int j = 0; j < CHUNK_A / 16 / 128; ++j) {
+            const int off = (ct + j * 128) * 16;
+            const uint4 v = *reinterpret_cast<const uint4*>(raw + off);
+            uint4 o;
+            o.x = to_tf32(__uint_as_float(v.x) - __uint_as_float(v.x & 0xffffe000u));
+            o.y = to_tf32(__uint_as_float(v.y) - __uint_as_float(v.y & 0xffffe000u));
+            o.z = to_tf32(__uint_as_float(v.z) - __uint_as_float(v.z & 0xffffe000u));
+            o.w = to_tf32(__uint_as_float(v.w) - __uint_as_float(v.w & 0xffffe000u));
+            *reinterpret_cast<uint4*>(lop + off) = o;
+            // the high part is written back truncated, so that it does not matter whether the tensor core
+            // truncates or rounds the 13 low mantissa bits of an fp32 word it is handed as tf32
+            *reinterpret_cast<uint4*>(raw + off) =
+                make_uint4(v.x & 0xffffe000u, v.y & 0xffffe000u, v.z & 0xffffe000u, v.w & 0xffffe000u);
+          }
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic stores -> tensor core's proxy
+          mbar_arrive(CONV(sw));
+        }
+      }
+    }
+  } else if (warp >= 8) {
+    // ---------------- epilogue ----------------
+    const int q = warp & 3;                          // TMEM lanes 32q .. 32q+31 belong to this warp
+    const int eg = (warp - 8) >> 2;                  // which of the NEG warps of this quadrant
+    uint8_t* my = stg + (warp - 8) * STG_BYTES;
+    const int64_t n4 = (p.N + 3) / 4;                // dropout hash groups per row
+    uint32_t tl = 0;
+    for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++tl) {
+      const uint32_t buf = tl & 1;
+      const int nt = (int)(t % p.ntiles);
+      const int64_t m0 = (t / p.ntiles) * BM + q * 32;
+      const int n0 = nt * BN;
+      const int64_t myrow = m0 + lane;
+      mbar_wait(TFULL(buf), (tl >> 1) & 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const uint32_t taddr0 = tmem_base + buf * BN + ((uint32_t)(q * 32) << 16);
+      bool released = false;
+#pragma unroll 1
+      for (int c0 = eg * 32; c0 < BN; c0 += NEG * 32) {
+        if (n0 + c0 >= p.N) break;                   // warp-uniform
+        uint32_t r[32];
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+            : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+              "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+            : "r"(taddr0 + (uint32_t)c0) : "memory");
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+            : "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+              "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+            : "r"(taddr0 + (uint32_t)(c0 + 16)) : "memory");
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        if (c0 + NEG * 32 >= BN || n0 + c0 + NEG * 32 >= p.N) {
+          // this warp's last read of the accumulator: hand the buffer back before the elementwise work
+          asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+          mbar_arrive(TEMPTY(buf));
+          released = true;
+        }
+        // ---- elementwise epilogue, thread = row, 32 consecutive columns in registers ----
+        const int colb = n0 + c0;
+        uint32_t min_word = 0xffffffffu;
+        if ((p.epi & GCNB_EPI_MASK) && myrow < p.M) min_word = p.mask_in[myrow * p.ldm + (colb >> 5)];
+        uint32_t out_word = 0;
+#pragma unroll
+        for (int g4 = 0; g4 < 8; ++g4) {
+          uint32_t h = 0;
+          if (p.epi & GCNB_EPI_DROPOUT) h = mix32((uint64_t)myrow * (uint64_t)n4 + (uint64_t)((colb >> 2) + g4), p.seed);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int j = g4 * 4 + e;
+            float x = __uint_as_float(r[j]);
+            const int col = colb + j;
+            if (col < p.N) {
+              if (p.epi & GCNB_EPI_BIAS) x += __ldg(p.bias + col);
+              if (p.epi & GCNB_EPI_RELU) x = fmaxf(x, 0.f);
+              if (p.epi & GCNB_EPI_DROPOUT) x = ((h >> (8 * e)) & 0xffu) >= p.keep_thresh ? x * p.scale : 0.f;
+              if (p.epi & GCNB_EPI_MASK) x = ((min_word >> j) & 1u) ? x * p.scale : 0.f;
+              if (x > 0.f) out_word |= 1u << j;
+            } else {
+              x = 0.f;
+            }
+            r[j] = __float_as_uint(x);
+          }
+        }
+        if (p.mask_out != nullptr && myrow < p.M) p.mask_out[myrow * p.ldm + (colb >> 5)] = out_word;
+        // ---- transpose through the private tile: 16-byte chunks, pitch 144 (conflict-free) ----
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<uint4*>(my + lane * STG_PITCH + j * 16) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+        __syncwarp();
+        // read back 4 rows x 128 bytes per instruction: full output lines
+        const int ch = lane & 7;
+        const int col = colb + ch * 4;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int rr = i * 4 + (lane >> 3);
+          const int64_t row = m0 + rr;
+          const float4 v = *reinterpret_cast<const float4*>(my + rr * STG_PITCH + ch * 16);
+          if (row < p.M && col < p.N) {
+            float* dp = p.D + row * p.ldd + col;
+            if (p.d_vec && col + 4 <= p.N) {
+              *reinterpret_cast<float4*>(dp) = v;
+            } else {
+              const float o[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e)
+                if (col + e < p.N) dp[e] = o[e];
+            }
+          }
+        }
+      }
+      if (!released) {   // this warp had no column group in the tile (N small): still a party of the barrier
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        mbar_arrive(TEMPTY(buf));
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1)
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+}
+
+// W -> per (n-tile, k-chunk) images { hi | lo }, each bn rows (n) x 128 bytes (32 k), 16-byte chunks XOR-swizzled
+// with the row like the TMA's SWIZZLE_128B; round-to-nearest split.  One thread per (n, k).
+__global__ void __launch_bounds__(256)
+xs_prep_w_kernel(const float* __restrict__ W, int64_t ldw, int trans_w, int N, int K, int bn, int nkc, int ntiles,
+                 uint8_t* __restrict__ img) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t kpad = (int64_t)nkc * KC, npad = (int64_t)ntiles * bn;
+  if (idx >= kpad * npad) return;
+  int k, n;   // fastest index follows the contiguous direction of the stored matrix
+  if (trans_w) { k = (int)(idx % kpad); n = (int)(idx / kpad); }
+  else         { n = (int)(idx % npad); k = (int)(idx / npad); }
+  float v = 0.f;
+  if (n < N && k < K) v = trans_w ? W[(int64_t)n * ldw + k] : W[(int64_t)k * ldw + n];
+  const int nt = n / bn, row = n % bn, kc = k / KC, kk = k % KC;
+  uint8_t* tile = img + ((int64_t)nt * nkc + kc) * (2 * (int64_t)bn * 128);
+  const int off = row * 128 + ((((kk >> 2) ^ (row & 7)) & 7) << 4) + (kk & 3) * 4;
+  const uint32_t hi = to_tf32(v);
+  *reinterpret_cast<uint32_t*>(tile + off) = hi;
+  *reinterpret_cast<uint32_t*>(tile + (int64_t)bn * 128 + off) = to_tf32(v - __uint_as_float(hi));
+}
+
+}  // namespace xs
+}  // namespace gcnb
+
+// ---- host side ---------------------------------------------------------------------------------------
+namespace gcnb {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled() {
+  static std::atomic<EncodeTiledFn> fn{nullptr};
+  EncodeTiledFn f = fn.load(std::memory_order_acquire);
+  if (!f) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      f = (EncodeTiledFn)ptr;
+    fn.store(f, std::memory_order_release);
+  }
+  return f;
+}
+
+template <int BN, int MODE>
+static int xs_launch(const CUtensorMap& tmap, const xs::Params& p, int grid, cudaStream_t stream) {
+  static std::atomic<uint64_t> configured{0};   // per-device opt-in to > 48 KB of dynamic shared memory
+  int dev = 0;
+  GCNB_CHECK_CUDA(cudaGetDevice(&dev));
+  const uint64_t bit = 1ull << (dev & 63);
+  if (dev >= 64 || !(configured.load(std::memory_order_relaxed) & bit)) {
+    GCNB_CHECK_CUDA(cudaFuncSetAttribute(xs::xs_kernel<BN, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         xs::smem_bytes(BN)));
+    configured.fetch_or(bit, std::memory_order_relaxed);
+  }
+  xs::xs_kernel<BN, MODE><<<grid, xs::threads_for(BN), xs::smem_bytes(BN), stream>>>(tmap, p);
+  GCNB_CHECK_CUDA(cudaGetLastError());
+  return GCNB_OK;
+}
+
+// Returns GCNB_OK when the product ran here, 1 when the shape is not this kernel's (caller falls back).
+int xw_stream_run(const float* X, int64_t ldx, const float* W, int64_t ldw, int trans_w, float* D, int64_t ldd,
+                  int64_t M, int N, int K, const float* bias, int epi, const uint32_t* mask_in, uint32_t* mask_out,
+                  int64_t ldm, float drop_p, uint32_t seed, int precision, int n_sm, cudaStream_t stream) {
+  static const int enabled = getenv("GCNB_XW_STREAM") ? atoi(getenv("GCNB_XW_STREAM")) : 1;
+  if (!enabled || precision > 1 || M < 1024 || K < 1 || K > 4096 || N < 1) return 1;
+  if (((uintptr_t)X & 15) || (ldx % 4) != 0 || M >= ((int64_t)1 << 31)) return 1;
+  EncodeTiledFn enc = encode_tiled();
+  if (!enc) return 1;
+  const int bn = N <= 64 ? 64 : 128;
+  const int ntiles = (N + bn - 1) / bn;
+  const int nkc = (K + xs::KC - 1) / xs::KC;
+  CUtensorMap tmap;
+  const cuuint64_t gdim[2] = {(cuuint64_t)K, (cuuint64_t)M};
+  const cuuint64_t gstride[1] = {(cuuint64_t)ldx * 4};
+  const cuuint32_t box[2] = {(cuuint32_t)xs::KC, (cuuint32_t)xs::BM};
+  const cuuint32_t estr[2] = {1, 1};
+  if (enc(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)X, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+          CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+    return 1;
+  uint8_t* img = nullptr;
+  const size_t img_bytes = (size_t)ntiles * nkc * xs::w_chunk(bn);
+  GCNB_CHECK_CUDA(cudaMallocAsync(&img, img_bytes, stream));
+  {
+    const int64_t total = (int64_t)ntiles * bn * nkc * xs::KC;
+    xs::xs_prep_w_kernel<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(W, ldw, trans_w, N, K, bn, nkc, ntiles, img);
+    if (cudaGetLastError() != cudaSuccess) { cudaFreeAsync(img, stream); return set_error(GCNB_ERR_CUDA, "xs_prep_w_kernel launch failed"); }
+  }
+  xs::Params p;
+  p.w_img = img; p.D = D; p.ldd = ldd; p.mask_in = mask_in; p.mask_out = mask_out; p.ldm = ldm; p.bias = bias;
+  p.M = M; p.N = N; p.K = K; p.nkc = nkc; p.ntiles = ntiles; p.mtiles = (M + xs::BM - 1) / xs::BM;
+  p.epi = epi;
+  p.keep_thresh = xs::drop_thresh(drop_p);
+  p.scale = (epi & (GCNB_EPI_DROPOUT | GCNB_EPI_MASK)) ? 256.f / (256.f - (float)p.keep_thresh) : 1.f;
+  p.seed = seed;
+  p.d_vec = (((uintptr_t)D & 15) == 0) && (ldd % 4 == 0) && (N % 4 == 0);
+  const int64_t tiles = p.mtiles * ntiles;
+  const int grid = (int)std::min<int64_t>(tiles, n_sm);
+  int rc;
+  if (precision == 0) rc = bn == 64 ? xs_launch<64, 0>(tmap, p, grid, stream) : xs_launch<128, 0>(tmap, p, grid, stream);
+  else rc = bn == 64 ? xs_launch<64, 1>(tmap, p, grid, stream) : xs_launch<128, 1>(tmap, p, grid, stream);
+  cudaFreeAsync(img, stream);
+  return rc;
+}
+
+// the keep decision of GCNB_EPI_DROPOUT, exported for tests: 1 when element (row, col) of an M x N output is kept
+extern "C" int gcnb_dropout_keeps(int64_t row, int col, int N, float p, uint32_t seed) {
+  const int64_t n4 = (N + 3) / 4;
+  const uint32_t h = xs::mix32((uint64_t)row * (uint64_t)n4 + (uint64_t)(col >> 2), seed);
+  return ((h >> (8 * (col & 3))) & 0xffu) >= xs::drop_thresh(p) ? 1 : 0;
+}
+
+}  // namespace gcnb

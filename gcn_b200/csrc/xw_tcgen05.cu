@@ -512,12 +512,67 @@ inline bool aligned16(const void* p) { return ((uintptr_t)p & 15) == 0; }
 
 }  // namespace
 
+namespace gcnb {
+int xw_stream_run(const float* X, int64_t ldx, const float* W, int64_t ldw, int trans_w, float* D, int64_t ldd,
+                  int64_t M, int N, int K, const float* bias, int epi, const uint32_t* mask_in, uint32_t* mask_out,
+                  int64_t ldm, float drop_p, uint32_t seed, int precision, int n_sm, cudaStream_t stream);   // xw_stream.cu
+// elementwise tail of gcnb_xw_ex for the products that do not run on the streaming kernel: one thread per
+// (row, 32-column word of the bit masks); same dropout hash (one word per 4 columns, one byte per element)
+__global__ void __launch_bounds__(256)
+xw_tail_kernel(float* __restrict__ D, int64_t ldd, const uint32_t* __restrict__ mask_in, uint32_t* __restrict__ mask_out,
+               int64_t ldm, int64_t M, int N, int epi, float scale, uint32_t thresh, uint32_t seed) {
+  const int words = (N + 31) / 32;
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= M * words) return;
+  const int64_t r = idx / words;
+  const int w = (int)(idx % words);
+  const int64_t n4 = (N + 3) / 4;
+  const uint32_t min_word = (epi & GCNB_EPI_MASK) ? mask_in[r * ldm + w] : 0xffffffffu;
+  uint32_t out_word = 0;
+  for (int j = 0; j < 32; ++j) {
+    const int c = w * 32 + j;
+    if (c >= N) break;
+    float x = D[r * ldd + c];
+    if (epi & GCNB_EPI_DROPOUT) {
+      const uint64_t g = (uint64_t)r * (uint64_t)n4 + (uint64_t)(c >> 2);
+      uint32_t a = (uint32_t)g ^ seed, b = (uint32_t)(g >> 32) + 0x9e3779b9u * (seed | 1u);
+      a *= 0x85ebca6bu; a ^= a >> 13; a += b; a *= 0xc2b2ae35u; a ^= a >> 16; a *= 0x27d4eb2fu; a ^= a >> 15;
+      x = ((a >> (8 * (c & 3))) & 0xffu) >= thresh ? x * scale : 0.f;
+    }
+    if (epi & GCNB_EPI_MASK) x = ((min_word >> j) & 1u) ? x * scale : 0.f;
+    if (x > 0.f) out_word |= 1u << j;
+    D[r * ldd + c] = x;
+  }
+  if (mask_out) mask_out[r * ldm + w] = out_word;
+}
+}  // namespace gcnb
+
+extern "C" int gcnb_xw_ex(const float* X, int64_t ldx, int trans_x, const float* W, int64_t ldw, int trans_w,
+                          float* D, int64_t ldd, int64_t M, int N, int K, const float* bias, int epilogue,
+                          const uint32_t* mask_in, uint32_t* mask_out, int64_t ldm, float drop_p, uint32_t seed,
+                          int precision, void* stream_);
+
 extern "C" int gcnb_xw(const float* X, int64_t ldx, int trans_x, const float* W, int64_t ldw, int trans_w,
                        float* D, int64_t ldd, int64_t M, int N, int K, const float* bias, int epilogue,
                        int precision, void* stream_) {
+  GCNB_REQUIRE((epilogue & ~(GCNB_EPI_BIAS | GCNB_EPI_RELU)) == 0, "unknown epilogue flags %d", epilogue);
+  return gcnb_xw_ex(X, ldx, trans_x, W, ldw, trans_w, D, ldd, M, N, K, bias, epilogue, nullptr, nullptr, 0, 0.f, 0,
+                    precision, stream_);
+}
+
+extern "C" int gcnb_xw_ex(const float* X, int64_t ldx, int trans_x, const float* W, int64_t ldw, int trans_w,
+                          float* D, int64_t ldd, int64_t M, int N, int K, const float* bias, int epilogue_ex,
+                          const uint32_t* mask_in, uint32_t* mask_out, int64_t ldm, float drop_p, uint32_t seed,
+                          int precision, void* stream_) {
   GCNB_REQUIRE(M >= 0 && N >= 0 && K >= 0, "negative size (M=%lld N=%d K=%d)", (long long)M, N, K);
   GCNB_REQUIRE(precision >= 0 && precision <= 2, "precision %d not in 0..2", precision);
-  GCNB_REQUIRE((epilogue & ~(GCNB_EPI_BIAS | GCNB_EPI_RELU)) == 0, "unknown epilogue flags %d", epilogue);
+  GCNB_REQUIRE((epilogue_ex & ~(GCNB_EPI_BIAS | GCNB_EPI_RELU | GCNB_EPI_DROPOUT | GCNB_EPI_MASK)) == 0,
+               "unknown epilogue flags %d", epilogue_ex);
+  GCNB_REQUIRE(!(epilogue_ex & GCNB_EPI_MASK) || mask_in != nullptr, "GCNB_EPI_MASK without mask_in");
+  GCNB_REQUIRE((mask_in == nullptr && mask_out == nullptr) || ldm >= (N + 31) / 32, "ldm smaller than ceil(N/32) words");
+  GCNB_REQUIRE(drop_p >= 0.f && drop_p < 1.f, "dropout probability %f not in [0, 1)", (double)drop_p);
+  const int epilogue = epilogue_ex & (GCNB_EPI_BIAS | GCNB_EPI_RELU);
+  const int tail = (epilogue_ex & (GCNB_EPI_DROPOUT | GCNB_EPI_MASK)) | (mask_out ? 0x100 : 0);
   GCNB_REQUIRE(!(epilogue & GCNB_EPI_BIAS) || bias != nullptr, "GCNB_EPI_BIAS without a bias pointer");
   if (M == 0 || N == 0) return GCNB_OK;
   GCNB_REQUIRE(D != nullptr && ldd >= N, "D is null or ldd < N");
@@ -532,13 +587,30 @@ extern "C" int gcnb_xw(const float* X, int64_t ldx, int trans_x, const float* W,
   DeviceGuard guard(dev);
   GCNB_CHECK_CUDA(guard.status);
   cudaStream_t stream = (cudaStream_t)stream_;
+  // elementwise tail (dropout / mask) as its own pass, for the products the streaming kernel does not take
+  auto run_tail = [&]() -> int {
+    if (!tail) return GCNB_OK;
+    const int64_t total = M * ((N + 31) / 32);
+    int t8 = (int)(drop_p * 256.f + 0.5f);
+    t8 = t8 < 0 ? 0 : (t8 > 255 ? 255 : t8);
+    xw_tail_kernel<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(D, ldd, mask_in, mask_out, ldm, M, N, tail & 0xff,
+                                                                          256.f / (256.f - (float)t8), (uint32_t)t8, seed);
+    GCNB_CHECK_CUDA(cudaGetLastError());
+    return GCNB_OK;
+  };
+
+  if (K > 0 && !trans_x) {
+    const int r = xw_stream_run(X, ldx, W, ldw, trans_w, D, ldd, M, N, K, bias, epilogue_ex, mask_in, mask_out, ldm,
+                                drop_p, seed, precision, sm_count(dev), stream);
+    if (r != 1) return r;   // ran (or failed) there; 1 = not that kernel's shape
+  }
 
   if (K == 0) {   // empty sum: D = epilogue(0)
     const int64_t total = M * N;
     xw::xw_reduce_kernel<<<(unsigned)((total + xw::kReduceElems - 1) / xw::kReduceElems), xw::kReduceElems * xw::kReduceLanes, 0, stream>>>(
         nullptr, 0, M, N, D, ldd, bias, epilogue);
     GCNB_CHECK_CUDA(cudaGetLastError());
-    return GCNB_OK;
+    return run_tail();
   }
 
   // N > 128: a 256-wide tile would convert X once instead of once per 128-wide n-tile, but its 131 KB of
@@ -615,5 +687,6 @@ extern "C" int gcnb_xw(const float* X, int64_t ldx, int trans_x, const float* W,
   }
   if (img) cudaFreeAsync(img, stream);
   if (partial) cudaFreeAsync(partial, stream);
+  if (rc == GCNB_OK) rc = run_tail();
   return rc;
 }

@@ -412,10 +412,29 @@ class PartitionedGCN(torch.nn.Module):
         self.optimizer = torch.optim.Adam(self.parameters(), lr=lr, weight_decay=weight_decay)
 
     def forward(self, x_local):
+        logits, nc = self.forward_logits(x_local)
+        return torch.nn.functional.log_softmax(logits[:, :nc] if logits.shape[1] != nc else logits, dim=1)
+
+    def forward_logits(self, x_local):
+        """(logits, nclass) of this rank's rows; `logits` may carry zero padding columns past nclass."""
         from . import gemm
         F = torch.nn.functional
         nfeat, nhid = self.gc1.weight.shape
         nclass = self.gc2.weight.shape[1]
+        if (self.association == "auto" and nfeat <= nhid and nclass < nhid
+                and not torch.cuda.is_current_stream_capturing()):
+            # fused dense block between the cached Â·X and the layer-2 aggregation (gcn_b200.gemm.mlp2)
+            if self._ax is None or self._ax[0] is not x_local or self._ax[1] != x_local._version:
+                with torch.no_grad():
+                    self._ax = (x_local, x_local._version, self.part.forward(x_local))
+            pad = (-nclass) % 4
+            w = F.pad(self.gc2.weight, (0, pad)) if pad else self.gc2.weight
+            self._drop_step = getattr(self, "_drop_step", 0) + 1
+            seed = (torch.initial_seed() * 2654435761 + 7919 * self.part.rank + self._drop_step) & 0xFFFFFFFF
+            s2 = gemm.mlp2(self._ax[2], self.gc1.weight, self.gc1.bias, w, p=self.dropout, seed=seed,
+                           training=self.training, out=self.part.next_operand(nclass + pad))
+            b2 = F.pad(self.gc2.bias, (0, pad)) if pad else self.gc2.bias
+            return spmm(self.part, s2) + b2, nclass
         if self.association == "auto" and nfeat <= nhid:
             if self._ax is None or self._ax[0] is not x_local or self._ax[1] != x_local._version:
                 with torch.no_grad():   # Â·X once: X is constant over the epochs
@@ -429,20 +448,31 @@ class PartitionedGCN(torch.nn.Module):
             pad = (-nclass) % 4
             w = F.pad(self.gc2.weight, (0, pad)) if pad else self.gc2.weight
             s2 = gemm.xw(h, w, out=self.part.next_operand(nclass + pad))
-            out = spmm(self.part, s2)[:, :nclass] + self.gc2.bias
+            b2 = F.pad(self.gc2.bias, (0, pad)) if pad else self.gc2.bias
+            out = spmm(self.part, s2) + b2
         else:
             s2 = spmm(self.part, h)
             out = gemm.xw(s2, self.gc2.weight, bias=self.gc2.bias)
-        return F.log_softmax(out, dim=1)
+        return out, nclass
 
     def step(self, x_local, labels_local, idx_train_local, n_train_global):
         """One training epoch (forward, NLL on the local training rows, backward, gradient
         all-reduce, Adam).  Returns the local loss contribution (sum / global count)."""
         self.train()
         self.optimizer.zero_grad(set_to_none=True)
-        out = self.forward(x_local)
-        loss = torch.nn.functional.nll_loss(out[idx_train_local], labels_local[idx_train_local],
-                                            reduction="sum") / n_train_global
+        logits, nc = self.forward_logits(x_local)
+        if logits.is_cuda:   # fused log-softmax + NLL (ops.logsoftmax_nll); the divisor is the GLOBAL training count
+            cache = getattr(self, "_train_mask", None)
+            if cache is None or cache[0] is not idx_train_local:
+                m = torch.zeros(logits.shape[0], dtype=torch.uint8, device=logits.device)
+                m[idx_train_local] = 1
+                cache = self._train_mask = (idx_train_local, m)
+            _, loss = ops.logsoftmax_nll(logits.contiguous(), nc, labels_local, idx_train_local, is_train=cache[1],
+                                         denom=n_train_global)
+        else:
+            out = torch.nn.functional.log_softmax(logits[:, :nc], dim=1)
+            loss = torch.nn.functional.nll_loss(out[idx_train_local], labels_local[idx_train_local],
+                                                reduction="sum") / n_train_global
         loss.backward()
         allreduce_grads(self, self.part.group)
         self.optimizer.step()

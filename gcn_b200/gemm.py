@@ -27,9 +27,13 @@ def _row_major(t: torch.Tensor) -> torch.Tensor:
 
 
 def gemm_raw(A: torch.Tensor, B: torch.Tensor, trans_a=False, trans_b=False, bias=None, relu=False,
-             precision=PRECISION_3XTF32, out=None) -> torch.Tensor:
-    """D = op(A)·op(B) (+bias)(ReLU) on tensor cores, no autograd.  A, B float32 CUDA matrices
-    (row-major, any leading dimension); op = transpose when the flag is set."""
+             precision=PRECISION_3XTF32, out=None, dropout=None, mask=None, mask_out=None) -> torch.Tensor:
+    """D = op(A)·op(B) (+bias)(ReLU)(dropout)(mask) on tensor cores, no autograd.  A, B float32 CUDA
+    matrices (row-major, any leading dimension); op = transpose when the flag is set.
+    dropout = (p, seed): after bias/ReLU, D = keep ? D / (1-p) : 0, keep bits from a counter hash, p quantised
+    to 1/256 (gcnb_xw_ex, GCNB_EPI_DROPOUT).  mask_out: int32 tensor [M, ceil(N/32)] receiving the bits
+    [D > 0].  mask = (bits, p): D = bit ? D / (1-p) : 0 (GCNB_EPI_MASK) — the backward of ReLU followed by
+    dropout, with the bits its forward product wrote."""
     for t, nm in ((A, "A"), (B, "B")):
         if not t.is_cuda:
             raise RuntimeError(f"gcn_b200: GEMM operand {nm} is on '{t.device}'; CUDA only, no CPU fallback")
@@ -53,13 +57,108 @@ def gemm_raw(A: torch.Tensor, B: torch.Tensor, trans_a=False, trans_b=False, bia
         epi |= _ffi.EPI_BIAS
     if relu:
         epi |= _ffi.EPI_RELU
+    words = (N + 31) // 32
+
+    def _bits(t, what):
+        if t.dtype != torch.int32 or tuple(t.shape) != (M, words) or not t.is_contiguous() or t.device != A.device:
+            raise ValueError(f"{what} must be a contiguous int32 tensor of shape (M, ceil(N/32)) on the operands' device")
+        return ctypes.c_void_p(t.data_ptr())
+
+    min_ptr = mout_ptr = None
+    p_drop, seed = 0.0, 0
+    if dropout is not None:
+        p_drop, seed = float(dropout[0]), int(dropout[1]) & 0xFFFFFFFF
+        if p_drop > 0.0:
+            epi |= _ffi.EPI_DROPOUT
+    if mask is not None:
+        bits, p_mask = mask
+        if dropout is not None and p_drop > 0.0 and float(p_mask) != p_drop:
+            raise ValueError("dropout and mask share one scale 1/(1-p)")
+        min_ptr, p_drop = _bits(bits, "mask bits"), float(p_mask)
+        epi |= _ffi.EPI_MASK
+    if mask_out is not None:
+        mout_ptr = _bits(mask_out, "mask_out")
     stream = ctypes.c_void_p(torch.cuda.current_stream(A.device).cuda_stream)
     with torch.cuda.device(A.device):
-        _ffi.call("gcnb_xw", ctypes.c_void_p(A.data_ptr()), A.stride(0), int(trans_a),
+        _ffi.call("gcnb_xw_ex", ctypes.c_void_p(A.data_ptr()), A.stride(0), int(trans_a),
                   ctypes.c_void_p(B.data_ptr()), B.stride(0), int(trans_b),
                   ctypes.c_void_p(out.data_ptr()), out.stride(0), M, N, K, bias_ptr, epi,
-                  int(precision), stream)
+                  min_ptr, mout_ptr, words, p_drop, seed, int(precision), stream)
     return out
+
+
+def unpack_mask_bits(bits: torch.Tensor, N: int) -> torch.Tensor:
+    """[M, ceil(N/32)] int32 words -> [M, N] bool (bit c % 32 of word c // 32)."""
+    M = bits.shape[0]
+    sh = torch.arange(32, device=bits.device, dtype=torch.int64)
+    b = ((bits.to(torch.int64).unsqueeze(-1) >> sh) & 1).bool().reshape(M, -1)
+    return b[:, :N]
+
+
+def dropout_keep_mask(M: int, N: int, p: float, seed: int) -> torch.Tensor:
+    """The keep mask GCNB_EPI_DROPOUT draws for an M x N output (host restatement through
+    gcnb_dropout_keeps, element by element — for tests on small shapes)."""
+    out = torch.empty((M, N), dtype=torch.bool)
+    for r in range(M):
+        for c in range(N):
+            out[r, c] = bool(_ffi.lib.gcnb_dropout_keeps(r, c, N, p, seed & 0xFFFFFFFF))
+    return out
+
+
+class _MLP2(torch.autograd.Function):
+    """s2 = dropout(relu(X·W1 + b1)) · W2 — the dense part of the 2-layer GCN between the two aggregations
+    when both layers run in the min-width association (gcn_b200.model), as ONE autograd node so that the
+    elementwise neighbours of the products ride in their epilogues:
+      forward   h  = xw_ex(X, W1, b1, ReLU | DROPOUT)          (replaces mm, +bias, relu, F.dropout: gcn6.py:131,142,245-246)
+                s2 = xw(h, W2)
+      backward  dW2  = hᵀ·g
+                dpre = xw_ex(g, W2ᵀ, MASK bits)                ((g·W2ᵀ) ⊙ [h > 0] / (1-p): dropout and ReLU backward)
+                dW1  = Xᵀ·dpre,  db1 = Σ_rows dpre,  dX = dpre·W1ᵀ (when X needs it)
+    h > 0 holds exactly where the unit was kept by the dropout AND passed the ReLU, so one bit per element,
+    written by the first product's epilogue, is the whole backward mask (1/32 of a word per element instead of
+    re-reading the activation)."""
+
+    @staticmethod
+    def forward(ctx, X, W1, b1, W2, p, seed, training, precision, out):
+        p_eff = float(p) if training else 0.0
+        bits = torch.empty((X.shape[0], (W1.shape[1] + 31) // 32), dtype=torch.int32, device=X.device)
+        h = gemm_raw(X.detach(), W1.detach(), bias=None if b1 is None else b1.detach(), relu=True,
+                     precision=precision, dropout=(p_eff, seed), mask_out=bits)
+        s2 = gemm_raw(h, W2.detach(), precision=precision, out=out)
+        ctx.p, ctx.precision, ctx.has_bias = p_eff, precision, b1 is not None
+        ctx.save_for_backward(X, W1, W2, h, bits)
+        return s2
+
+    @staticmethod
+    def backward(ctx, g):
+        X, W1, W2, h, bits = ctx.saved_tensors
+        g = g.to(torch.float32)
+        if g.stride(1) != 1:
+            g = g.contiguous()
+        gX = gW1 = gb1 = gW2 = None
+        if ctx.needs_input_grad[3]:
+            gW2 = _dw(h, g, ctx.precision)
+        dpre = gemm_raw(g, W2.detach(), trans_b=True, precision=ctx.precision, mask=(bits, ctx.p))
+        if ctx.needs_input_grad[1]:
+            gW1 = _dw(X.detach(), dpre, ctx.precision)
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            gb1 = dpre.sum(dim=0)
+        if ctx.needs_input_grad[0]:
+            gX = gemm_raw(dpre, W1.detach(), trans_b=True, precision=ctx.precision)
+        return gX, gW1, gb1, gW2, None, None, None, None, None
+
+
+def _dw(X, g, precision):
+    """Xᵀ·g with the narrower operand second (see _XW.backward)."""
+    if X.shape[1] < g.shape[1] and _SWAP_DW:
+        return gemm_raw(g, X, trans_a=True, precision=precision).t().contiguous()
+    return gemm_raw(X, g, trans_a=True, precision=precision)
+
+
+def mlp2(X, W1, b1, W2, p=0.5, seed=0, training=True, precision=PRECISION_3XTF32, out=None):
+    """``dropout(relu(X @ W1 + b1), p) @ W2`` with autograd, three fused tensor-core products forward+backward
+    plus the two weight-gradient products (see :class:`_MLP2`)."""
+    return _MLP2.apply(X, W1, b1, W2, float(p), int(seed), bool(training), int(precision), out)
 
 
 class _XW(torch.autograd.Function):

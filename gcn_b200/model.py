@@ -79,12 +79,18 @@ class GCN(nn.Module):
 
     def forward(self, x, adj, name="dataset"):
         """adj: normalised adjacency (torch sparse tensor on the GPU or an SpmmPlan)."""
+        logits, nc = self.forward_logits(x, adj)
+        return F.log_softmax(logits[:, :nc] if logits.shape[1] != nc else logits, dim=1)
+
+    def forward_logits(self, x, adj):
+        """(logits, nclass): the class scores before log-softmax; `logits` may carry zero padding columns
+        past nclass (the aggregation runs at a multiple of 4 columns)."""
         if self.association == "auto":
             return self._forward_min_width(x, adj)
         x = self.gc1(x, adj, relu=self.with_relu)
         x = F.dropout(x, self.dropout, training=self.training)
         x = self.gc2(x, adj)
-        return F.log_softmax(x, dim=1)
+        return x, x.shape[1]
 
     def invalidate_cache(self):
         """Forget the cached Â·X (call after changing the features in place)."""
@@ -101,6 +107,23 @@ class GCN(nn.Module):
 
     def _forward_min_width(self, x, adj):
         nfeat, nhid = self.gc1.weight.shape
+        nh, nc = self.gc2.weight.shape
+        if (not _is_sparse(x) and not x.requires_grad and nfeat <= nhid and nc < nh and self.with_relu
+                and not torch.cuda.is_current_stream_capturing()):
+            # both layers in the min-width association: everything between the cached Â·X and the layer-2
+            # aggregation is ONE fused block — (Â·X)·W1 + b1, ReLU, dropout in the first product's epilogue,
+            # ·W2 next, dropout/ReLU backward in the epilogue of dS·W2ᵀ (gcn_b200.gemm.mlp2).  Under CUDA-graph
+            # capture the seed would be frozen into the graph, so capture takes the unfused path below.
+            pad = (-nc) % 4
+            w2 = F.pad(self.gc2.weight, (0, pad)) if pad else self.gc2.weight
+            b2 = self.gc2.bias
+            if b2 is not None and pad:
+                b2 = F.pad(b2, (0, pad))
+            self._drop_step = getattr(self, "_drop_step", 0) + 1
+            seed = (torch.initial_seed() * 2654435761 + self._drop_step) & 0xFFFFFFFF
+            s2 = gemm.mlp2(self._aggregated_features(x, adj), self.gc1.weight, self.gc1.bias, w2,
+                           p=self.dropout, seed=seed, training=self.training)
+            return ops.spmm(adj, s2, bias=b2), nc
         if not _is_sparse(x) and not x.requires_grad and nfeat <= nhid:
             # (Â·X)·W1 + b1 with Â·X cached: no SpMM in layer 1, forward or backward
             h = gemm.xw(self._aggregated_features(x, adj), self.gc1.weight, bias=self.gc1.bias,
@@ -108,7 +131,6 @@ class GCN(nn.Module):
         else:
             h = self.gc1(x, adj, relu=self.with_relu) if isinstance(self.gc1, GraphConvolution) else self.gc1(x, adj)
         h = F.dropout(h, self.dropout, training=self.training)
-        nh, nc = self.gc2.weight.shape
         if nc < nh:
             # Â·(H·W2) + b2: SpMM at width nclass (zero-padded to 4 floats for 128-bit rows)
             pad = (-nc) % 4
@@ -117,11 +139,9 @@ class GCN(nn.Module):
             if b is not None and pad:
                 b = F.pad(b, (0, pad))
             out = ops.spmm(adj, gemm.xw(h, w), bias=b)
-            if pad:
-                out = out[:, :nc]
         else:
             out = self.gc2(h, adj)
-        return F.log_softmax(out, dim=1)
+        return out, nc
 
     def initialize(self):
         self.gc1.reset_parameters()
@@ -208,11 +228,23 @@ class GCN(nn.Module):
         else:
             self._train_with_val(self.labels, idx_train, idx_val, train_iters, verbose)
 
+    def _loss(self, labels, idx_train):
+        """(output, loss) of one forward pass: log-softmax over all vertices + NLL on idx_train, fused
+        (ops.logsoftmax_nll: gcn6.py:248 + :427 in one pass forward, one pass backward)."""
+        logits, nc = self.forward_logits(self.features, self.adj_norm)
+        if logits.stride(1) != 1:
+            logits = logits.contiguous()
+        cache = getattr(self, "_train_mask", None)
+        if cache is None or cache[0] is not idx_train or cache[1].shape[0] != logits.shape[0]:
+            m = torch.zeros(logits.shape[0], dtype=torch.uint8, device=logits.device)
+            m[idx_train] = 1
+            cache = self._train_mask = (idx_train, m)
+        return ops.logsoftmax_nll(logits, nc, labels, idx_train, is_train=cache[1])
+
     def _step(self, optimizer, labels, idx_train):
         self.train()
         optimizer.zero_grad()
-        output = self.forward(self.features, self.adj_norm)
-        loss = F.nll_loss(output[idx_train], labels[idx_train])
+        output, loss = self._loss(labels, idx_train)
         loss.backward()
         optimizer.step()
         return output, loss
@@ -235,8 +267,7 @@ class GCN(nn.Module):
         graph_ = torch.cuda.CUDAGraph()
         self.train()
         with torch.cuda.graph(graph_):
-            output = self.forward(self.features, self.adj_norm)
-            loss = F.nll_loss(output[idx_train], labels[idx_train])
+            output, loss = self._loss(labels, idx_train)
             loss.backward()
             optimizer.step()
 

@@ -272,3 +272,59 @@ def spmm(adj, B: torch.Tensor, bias: torch.Tensor | None = None, relu: bool = Fa
     plan = plan_for(adj)
     _require_cuda(B, "the dense operand")
     return _SpMM.apply(plan, B, bias, bool(relu))
+
+
+# ---- fused head: log-softmax + NLL on the training vertices (gcnb_logsoftmax_nll_*) -------------------------
+class _LogSoftmaxNLL(torch.autograd.Function):
+    """(logp, loss) = (log_softmax(logits[:, :ncls]), nll_loss(logp[idx_train], labels[idx_train])) in one pass,
+    backward = one kernel writing dlogits in the (possibly padded) layout of `logits`.  Replaces F.log_softmax
+    (pygcn/gcn6.py:248) + F.nll_loss (gcn6.py:427) and their autograd chain.  `logp` is returned for the
+    caller (the model's output) and carries no gradient."""
+
+    @staticmethod
+    def forward(ctx, logits, ncls, labels, idx_train, is_train, denom):
+        n = logits.shape[0]
+        logp = torch.empty((n, ncls), dtype=torch.float32, device=logits.device)
+        loss = torch.empty((), dtype=torch.float32, device=logits.device)
+        with torch.cuda.device(logits.device):
+            _ffi.call("gcnb_logsoftmax_nll_fwd", ctypes.c_void_p(logits.data_ptr()), logits.stride(0), n, int(ncls),
+                      ctypes.c_void_p(labels.data_ptr()), ctypes.c_void_p(idx_train.data_ptr()), idx_train.numel(),
+                      int(denom), ctypes.c_void_p(logp.data_ptr()), logp.stride(0), ctypes.c_void_p(loss.data_ptr()),
+                      _stream_ptr(logits.device))
+        ctx.save_for_backward(logp, labels, is_train)
+        ctx.ncls, ctx.ncols, ctx.denom = int(ncls), logits.shape[1], int(denom)
+        ctx.mark_non_differentiable(logp)
+        return logp, loss
+
+    @staticmethod
+    def backward(ctx, _g_logp, g_loss):
+        logp, labels, is_train = ctx.saved_tensors
+        n = logp.shape[0]
+        dlogits = torch.empty((n, ctx.ncols), dtype=torch.float32, device=logp.device)
+        g = g_loss.to(torch.float32).contiguous()
+        with torch.cuda.device(logp.device):
+            _ffi.call("gcnb_logsoftmax_nll_bwd", ctypes.c_void_p(logp.data_ptr()), logp.stride(0),
+                      ctypes.c_void_p(labels.data_ptr()), ctypes.c_void_p(is_train.data_ptr()),
+                      ctypes.c_void_p(g.data_ptr()), ctx.denom, n, ctx.ncls, ctx.ncols,
+                      ctypes.c_void_p(dlogits.data_ptr()), dlogits.stride(0), _stream_ptr(logp.device))
+        return dlogits, None, None, None, None, None
+
+
+def logsoftmax_nll(logits: torch.Tensor, ncls: int, labels: torch.Tensor, idx_train: torch.Tensor,
+                   is_train: torch.Tensor | None = None, denom: int | None = None):
+    """``(F.log_softmax(logits[:, :ncls], 1), F.nll_loss(logp[idx_train], labels[idx_train]))`` fused.
+    logits: float32 CUDA [n, >= ncls] with contiguous rows (columns past ncls are padding); labels int64 [n];
+    idx_train int64 (distinct vertices); is_train: uint8/bool [n] membership of idx_train (built when omitted);
+    denom: divisor of the loss sum (default len(idx_train); the global count on a row partition)."""
+    _require_cuda(logits, "logits")
+    if logits.dtype != torch.float32 or logits.dim() != 2 or logits.stride(1) != 1 or logits.shape[1] < ncls:
+        raise ValueError("logits must be float32 [n, >= ncls] with contiguous rows")
+    labels = labels.to(torch.long).contiguous()
+    idx_train = idx_train.to(torch.long).contiguous()
+    if is_train is None:
+        is_train = torch.zeros(logits.shape[0], dtype=torch.uint8, device=logits.device)
+        is_train[idx_train] = 1
+    elif is_train.dtype == torch.bool:
+        is_train = is_train.view(torch.uint8)
+    return _LogSoftmaxNLL.apply(logits, int(ncls), labels, idx_train, is_train.contiguous(),
+                                idx_train.numel() if denom is None else int(denom))

@@ -134,6 +134,9 @@ def normalized_csr(src, dst, n, to_host=True):
     key = torch.cat((src * n + dst, dst * n + src, diag * n + diag))
     del src, dst, keep
     key = torch.unique(key)  # sorted: row-major, ascending columns
+    if key.numel() >= 2 ** 31 - 16:
+        raise ValueError(f"{key.numel()} non-zeros do not fit the int32 CSR offsets of one plan "
+                         "(include/gcn_b200.h: nnz < 2^31 - 16); partition the rows first")
     row = torch.div(key, n, rounding_mode="floor")
     col = key - row * n
     del key

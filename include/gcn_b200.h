@@ -44,6 +44,10 @@ extern "C" {
 #define GCNB_EPI_RELU 2
 #define GCNB_EPI_ACCUM 4 /* gcnb_spmm only: C = C + A·B (then bias/ReLU); used by the column-split
                             multi-GPU path, gcn_b200/dist.py */
+#define GCNB_EPI_DROPOUT 8 /* gcnb_xw_ex only: after bias/ReLU, out = keep ? out / (1-p) : 0, keep bits from a counter hash
+                              of (seed, row, col / 4), one byte per element, p quantised to 1/256  (F.dropout, gcn6.py:246) */
+#define GCNB_EPI_MASK 16   /* gcnb_xw_ex only: out = bit(mask_in, row, col) ? out / (1-p) : 0 — the backward of ReLU followed
+                              by dropout, with the bits the forward product wrote (autograd of gcn6.py:245-246) */
 
 /* plan flags */
 #define GCNB_PLAN_DEFAULT 0
@@ -114,6 +118,32 @@ int gcnb_permute_rows(const float* X, const int32_t* vomp, float* out, int64_t n
 int gcnb_xw(const float* X, int64_t ldx, int trans_x, const float* W, int64_t ldw, int trans_w,
             float* D, int64_t ldd, int64_t M, int N, int K, const float* bias, int epilogue,
             int precision, void* stream);
+/* gcnb_xw with the fused elementwise neighbours of the product in the GCN layer (same operands, plus):
+ *   GCNB_EPI_DROPOUT: dropout probability `drop_p` in [0,1), 32-bit `seed` (a new one per training step);
+ *   mask_out (optional, any epilogue): bit (row, col) of word mask_out[row * ldm + col / 32] = (out > 0) — for a
+ *                     ReLU / dropout forward this is the mask its backward needs, 1 bit per element;
+ *   GCNB_EPI_MASK:    mask_in in that layout and `drop_p` (scale 1/(1-p); 0 for a plain ReLU mask).
+ * gcnb_dropout_keeps returns the keep decision of one element (host function; tests restate the mask with it). */
+int gcnb_xw_ex(const float* X, int64_t ldx, int trans_x, const float* W, int64_t ldw, int trans_w,
+               float* D, int64_t ldd, int64_t M, int N, int K, const float* bias, int epilogue,
+               const uint32_t* mask_in, uint32_t* mask_out, int64_t ldm, float drop_p, uint32_t seed,
+               int precision, void* stream);
+int gcnb_dropout_keeps(int64_t row, int col, int N, float drop_p, uint32_t seed);
+
+/* Fused log-softmax + NLL of the GCN head (replaces F.log_softmax, pygcn/gcn6.py:248, and
+ * F.nll_loss(output[idx_train], labels[idx_train]), gcn6.py:427) and its gradient.  DEVICE pointers.
+ *   fwd: logp[r, 0..ncls) = log_softmax(logits[r, 0..ncls)) for all n rows;
+ *        loss[0] = -(1/denom) * sum_{i < n_train} logp[idx_train[i], labels[idx_train[i]]]  (fixed order)
+ *   bwd: dlogits[r, c] = gloss[0]/denom * (exp(logp[r,c]) - [c == labels[r]]) where is_train[r], else 0;
+ *        columns ncls..ncols-1 (padding of the aggregation width) are written as 0.
+ * labels / idx_train are int64 (torch.long), is_train one byte per vertex. */
+int gcnb_logsoftmax_nll_fwd(const float* logits, int64_t ldl, int64_t n, int ncls, const int64_t* labels,
+                            const int64_t* idx_train, int64_t n_train, int64_t denom, float* logp, int64_t ldo,
+                            float* loss, void* stream);
+int gcnb_logsoftmax_nll_bwd(const float* logp, int64_t ldo, const int64_t* labels, const uint8_t* is_train,
+                            const float* gloss, int64_t denom, int64_t n, int ncls, int ncols, float* dlogits,
+                            int64_t ldd, void* stream);
+
 
 /* ---------------------------------------------------------------------------------------------
  * Multi-GPU exchange over NVLink peer memory (the reference is single-GPU).

@@ -104,3 +104,87 @@ def test_xw_degenerate():
     assert gemm.gemm_raw(torch.randn(0, 3, device=DEV), torch.randn(3, 4, device=DEV)).shape == (0, 4)
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         gemm.gemm_raw(torch.randn(2, 2), torch.randn(2, 2))
+
+
+# ---- streaming kernel (xw_stream.cu): persistent warp-specialised tcgen05 kernel for M >> K, N --------------
+@pytest.mark.parametrize("M,N,K", [(2500, 256, 100), (100_000, 48, 256), (5000, 256, 48), (1024, 64, 32),
+                                   (3001, 47, 100), (1500, 130, 260), (20_000, 300, 36), (1100, 8, 4)])
+@pytest.mark.parametrize("precision", [0, 1])
+def test_xw_stream_shapes(M, N, K, precision, monkeypatch):
+    g = torch.Generator(device=DEV).manual_seed(M + N + K)
+    X = torch.randn(M, K, device=DEV, generator=g)
+    W = torch.randn(K, N, device=DEV, generator=g) / K ** 0.5
+    b = torch.randn(N, device=DEV, generator=g)
+    ref = X.double() @ W.double()
+    out = gemm.gemm_raw(X, W, precision=precision)
+    assert rel(out, ref) < TOL[precision]
+    assert rel(gemm.gemm_raw(X, W.t().contiguous(), trans_b=True, precision=precision), ref) < TOL[precision]
+    assert rel(gemm.gemm_raw(X, W, bias=b, relu=True, precision=precision), torch.relu(ref + b.double())) < TOL[precision]
+    # the first kernel on the same operands (GCNB_XW_STREAM is read once per process: compare through the
+    # transposed-X form, which always takes the first kernel)
+    old = gemm.gemm_raw(X.t().contiguous(), W, trans_a=True, precision=precision)
+    assert rel(old, ref) < TOL[precision]
+    # padded leading dimensions of X and D
+    big = torch.randn(M, K + 12, device=DEV, generator=g)
+    Xv = big[:, 4:4 + K]
+    dst = torch.full((M, N + 8), 3.0, device=DEV)
+    gemm.gemm_raw(Xv, W, out=dst[:, 4:4 + N] if N % 4 == 0 else dst[:, 1:1 + N], precision=precision)
+    got = dst[:, 4:4 + N] if N % 4 == 0 else dst[:, 1:1 + N]
+    assert rel(got, Xv.double() @ W.double()) < TOL[precision]
+    assert torch.all(dst[:, 0] == 3.0) and torch.all(dst[:, -1] == 3.0)
+
+
+def test_xw_fused_dropout_and_mask():
+    g = torch.Generator(device=DEV).manual_seed(11)
+    M, N, K = 1500, 24, 20
+    X = torch.randn(M, K, device=DEV, generator=g)
+    W = torch.randn(K, N, device=DEV, generator=g)
+    b = torch.randn(N, device=DEV, generator=g)
+    p, seed = 0.375, 12345     # multiples of 1/256 are exact (the kernel quantises p to 1/256)
+    keep = gemm.dropout_keep_mask(M, N, p, seed).to(DEV)
+    assert 0.58 < keep.float().mean().item() < 0.67
+    ref = torch.relu(X.double() @ W.double() + b.double()) * keep / (1 - p)
+    got = gemm.gemm_raw(X, W, bias=b, relu=True, dropout=(p, seed))
+    assert rel(got, ref) < 1e-5
+    assert not torch.equal(got, gemm.gemm_raw(X, W, bias=b, relu=True, dropout=(p, seed + 1)))   # another step, another mask
+    # the tail kernel of the first GEMM kernel draws the same mask (transposed-X form of the same product)
+    got_t = gemm.gemm_raw(X.t().contiguous(), W, trans_a=True, bias=b, relu=True, dropout=(p, seed))
+    assert rel(got_t, ref) < 1e-5
+    # the bit mask [out > 0] written next to the product, on both kernels
+    bits = torch.empty(M, (N + 31) // 32, dtype=torch.int32, device=DEV)
+    got2 = gemm.gemm_raw(X, W, bias=b, relu=True, dropout=(p, seed), mask_out=bits)
+    assert torch.equal(got2, got) and torch.equal(gemm.unpack_mask_bits(bits, N), got > 0)
+    bits_t = torch.empty_like(bits)
+    gemm.gemm_raw(X.t().contiguous(), W, trans_a=True, bias=b, relu=True, dropout=(p, seed), mask_out=bits_t)
+    assert torch.equal(gemm.unpack_mask_bits(bits_t, N), got_t > 0)
+    # mask epilogue: (G·W2) ⊙ bits / (1-p)  (G: M x K2, product M x N)
+    K2 = 40
+    G = torch.randn(M, K2, device=DEV, generator=g)
+    W2 = torch.randn(K2, N, device=DEV, generator=g)
+    refm = (G.double() @ W2.double()) * (got > 0) / (1 - p)
+    assert rel(gemm.gemm_raw(G, W2, mask=(bits, p)), refm) < 1e-5
+    assert rel(gemm.gemm_raw(G.t().contiguous(), W2, trans_a=True, mask=(bits, p)), refm) < 1e-5
+
+
+@pytest.mark.parametrize("p", [0.0, 0.5])
+def test_mlp2_block_matches_unfused_autograd(p):
+    """gemm.mlp2 (fused dense block of the 2-layer GCN) against torch autograd in fp64 with the SAME dropout mask."""
+    g = torch.Generator(device=DEV).manual_seed(17)
+    M, K, H, N = 4000, 36, 64, 12
+    X = torch.randn(M, K, device=DEV, generator=g)
+    W1 = (torch.randn(K, H, device=DEV, generator=g) / 6).requires_grad_(True)
+    b1 = torch.randn(H, device=DEV, generator=g).requires_grad_(True)
+    W2 = (torch.randn(H, N, device=DEV, generator=g) / 8).requires_grad_(True)
+    seed = 99
+    s2 = gemm.mlp2(X, W1, b1, W2, p=p, seed=seed, training=True)
+    G = torch.randn(M, N, device=DEV, generator=g)
+    s2.backward(G)
+    keep = (gemm.dropout_keep_mask(M, H, p, seed).to(DEV) if p > 0 else torch.ones(M, H, dtype=torch.bool, device=DEV))
+    W1r, b1r, W2r = (t.detach().double().requires_grad_(True) for t in (W1, b1, W2))
+    hr = torch.relu(X.double() @ W1r + b1r) * keep / (1 - p)
+    (hr @ W2r).backward(G.double())
+    assert rel(s2.detach(), (hr @ W2r).detach()) < 1e-5
+    assert rel(W1.grad, W1r.grad) < 2e-5 and rel(b1.grad, b1r.grad) < 2e-5 and rel(W2.grad, W2r.grad) < 2e-5
+    # eval mode: no dropout
+    s_eval = gemm.mlp2(X, W1, b1, W2, p=p, seed=seed, training=False)
+    assert rel(s_eval.detach(), (torch.relu(X.double() @ W1r + b1r) @ W2r).detach()) < 1e-5

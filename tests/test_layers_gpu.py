@@ -165,3 +165,56 @@ def test_cuda_graph_step_matches_eager(golden_gcn):
                            m.gc1.weight.detach().cpu().numpy())
     assert abs(losses[True][0] - losses[False][0]) < 1e-4
     assert rel_err(losses[True][1], losses[False][1]) < 1e-4
+
+
+def test_fused_logsoftmax_nll_matches_torch():
+    """ops.logsoftmax_nll (gcnb_logsoftmax_nll_fwd/bwd) against F.log_softmax + F.nll_loss and their autograd,
+    with padding columns in the logits (the aggregation runs at a multiple of 4 columns) and a custom divisor."""
+    g = torch.Generator(device=DEV).manual_seed(5)
+    n, ncls, ncols = 3001, 47, 48
+    logits = torch.randn(n, ncols, device=DEV, generator=g) * 3
+    logits[:, ncls:] = 0
+    labels = torch.randint(0, ncls, (n,), device=DEV, generator=g)
+    idx = torch.randperm(n, device=DEV, generator=g)[:517]
+    for denom in (None, 9999):
+        x = logits.clone().requires_grad_(True)
+        logp, loss = ops.logsoftmax_nll(x, ncls, labels, idx, denom=denom)
+        (loss * 1.7).backward()
+        xr = logits[:, :ncls].double().clone().requires_grad_(True)
+        ref_logp = F.log_softmax(xr, dim=1)
+        ref_loss = F.nll_loss(ref_logp[idx], labels[idx], reduction="sum") / (len(idx) if denom is None else denom)
+        (ref_loss * 1.7).backward()
+        assert rel_err(logp.cpu().numpy(), ref_logp.detach().cpu().numpy()) < 1e-6
+        assert abs(loss.item() - ref_loss.item()) < 1e-5 * max(1.0, abs(ref_loss.item()))
+        assert rel_err(x.grad[:, :ncls].cpu().numpy(), xr.grad.cpu().numpy()) < 1e-5
+        assert torch.all(x.grad[:, ncls:] == 0) and not logp.requires_grad
+        # bit-reproducible: fixed summation order
+        assert ops.logsoftmax_nll(logits, ncls, labels, idx, denom=denom)[1].item() == loss.item()
+
+
+def test_training_step_uses_fused_head_and_matches_unfused(golden_gcn):
+    """GCN._step (fused log-softmax + NLL, fused dense block in the 'auto' association) against the same model
+    evaluated with torch's own log_softmax / nll_loss on the logits: loss and every gradient."""
+    g = golden_gcn
+    n, a, feats = _load(g)
+    for assoc in ("reference", "auto"):
+        torch.manual_seed(3)
+        m = model.GCN(nfeat=24, nhid=32, nclass=7, dropout=0.0, device=DEV, association=assoc)
+        x = torch.randn(n, 24, device=DEV)
+        feats_t, plan, y, _ = m._prepare(x, a, g["labels"], True, None)
+        m.features, m.adj_norm, m.labels = feats_t, plan, y
+        idx = torch.from_numpy(g["idx_train"]).to(DEV)
+        m.train()
+        m.zero_grad()
+        out, loss = m._loss(y, idx)
+        loss.backward()
+        got = [p.grad.clone() for p in m.parameters()]
+        m.zero_grad()
+        logits, nc = m.forward_logits(feats_t, plan)
+        ref_out = F.log_softmax(logits[:, :nc], dim=1)
+        ref_loss = F.nll_loss(ref_out[idx], y[idx])
+        ref_loss.backward()
+        assert rel_err(out.detach().cpu().numpy(), ref_out.detach().cpu().numpy()) < 1e-5
+        assert abs(loss.item() - ref_loss.item()) < 1e-5
+        for a_, b_ in zip(got, [p.grad for p in m.parameters()]):
+            assert rel_err(a_.cpu().numpy(), b_.cpu().numpy()) < 2e-5
