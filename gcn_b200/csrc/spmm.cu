@@ -269,11 +269,14 @@ static int upload_matrix(const int32_t* rowptr, const int32_t* col, const float*
                                cudaMemcpyHostToDevice));
     M->bytes += (s_split_rows.size() + s_split_ptr.size()) * 4;
   }
-  // panel class: built when the mean row is long enough for rows of a panel to share columns, kept when
-  // the measured sharing (non-zeros per distinct column of a panel) says it pays.  GCNB_PANEL: -1 auto,
-  // 0 never, 1 always.
+  // panel class: OFF unless asked for (GCNB_PLAN_PANEL / GCNB_PANEL=1).  Measured on the Reddit-shaped graph
+  // (profiles/r02_b_*, r02_d_ncu_reddit_deg_*): it removes a third of the L2->SM bytes (L1 hit rate 16 % -> 42 %)
+  // and is no faster than the stream class (3.17 vs 3.09 ms in degree order) because an L1 hit occupies the LSU
+  // data pipe exactly like the miss it replaces; in an order that puts rows of very different length into one
+  // panel it is 10x slower (35.5 vs 3.43 ms).  GCNB_PANEL: 0 never (default), 1 always, -1 = the size /
+  // sharing rule below.
   {
-    static const int panel_env = getenv("GCNB_PANEL") ? atoi(getenv("GCNB_PANEL")) : -1;
+    static const int panel_env = getenv("GCNB_PANEL") ? atoi(getenv("GCNB_PANEL")) : 0;
     const int panel_mode = (flags & GCNB_PLAN_NO_PANEL) ? 0 : (flags & GCNB_PLAN_PANEL) ? 1 : panel_env;
     static const int tile_nnz = getenv("GCNB_PANEL_TILE") ? atoi(getenv("GCNB_PANEL_TILE")) : 512;
     static const int item_nnz = getenv("GCNB_PANEL_ITEM") ? atoi(getenv("GCNB_PANEL_ITEM")) : 32768;
@@ -544,17 +547,15 @@ static int launch_vec(const LaunchArgs& a) {
   if (nvec <= 8 && stream_min >= 8) return launch_one<TB, VEC, 8, 1>(a);
   if (nvec <= 16 && stream_min >= 16) return launch_one<TB, VEC, 16, 1>(a);
   if (nvec <= 32) return launch_one<TB, VEC, 32, 1>(a);
-  // wide rows: whole warp per row, NV vectors per lane, as few column tiles as possible — unless the
-  // gathered operand is re-used heavily (mean row >= 64 non-zeros) and does not fit L2 while a 32-vector
-  // column slice of it does: then one slice per grid.y (they run one after the other) keeps the slice
-  // L2-resident.  Measured on the Reddit-shaped graph at k = 602 (profiles/r02_d_ncu_reddit_deg_k602.txt):
-  // 71 GB of DRAM reads in 19.3 ms with two 384-column slices.  GCNB_WIDE_NV caps NV (0 = this rule).
+  // wide rows: whole warp per row, NV vectors per lane, as few column tiles as possible.  GCNB_WIDE_NV caps NV
+  // (more, narrower column slices in grid.y, which run one after the other): tried for the Reddit-shaped graph
+  // at k = 602, whose operand (561 MB) misses L2 (71 GB of DRAM reads per launch with two 384-column slices,
+  // profiles/r02_d_ncu_reddit_deg_k602.txt) — five 128-column slices were SLOWER (22.3 vs 20.7 ms,
+  // profiles/r02_e_reddit_k602_*): a 119 MB slice does not stay in the 126 MB L2 either and the (col,val)
+  // stream is re-read per slice.  So the cap stays an experiment switch (0 = none).
   static const int wide_nv = getenv("GCNB_WIDE_NV") ? atoi(getenv("GCNB_WIDE_NV")) : 0;
   int nvmax = NVMAX;
   if (wide_nv > 0) nvmax = std::min(NVMAX, wide_nv);
-  else if (a.M->nnz >= 64 * a.M->m && (double)a.M->n * a.k * sizeof(TB) > 100e6 &&
-           (double)a.M->n * 32 * VEC * sizeof(TB) <= 130e6)
-    nvmax = 1;
   const int tiles = (nvec + 32 * nvmax - 1) / (32 * nvmax);
   const int nv = (nvec + 32 * tiles - 1) / (32 * tiles);
   if (nv <= 1) return launch_one<TB, VEC, 32, 1>(a);

@@ -50,14 +50,18 @@ constexpr int STG_PITCH = 144;   // bytes per row of the epilogue's transpose ti
 constexpr int STG_BYTES = 32 * STG_PITCH;
 constexpr int SMEM_MAX = 232448; // 227 KB of dynamic shared memory per CTA
 
-__host__ __device__ constexpr int epi_warps(int bn) { return bn <= 64 ? 4 : 8; }
-__host__ __device__ constexpr int threads_for(int bn) { return (8 + epi_warps(bn)) * 32; }
+constexpr int NE = 8;            // epilogue warps (two per TMEM lane quadrant)
+constexpr int THREADS = (8 + NE) * 32;
+constexpr int RA_MAX = 12;       // most X chunks in flight (barrier slots)
 __host__ __device__ constexpr int w_chunk(int bn) { return 2 * bn * 128; }      // hi | lo
-__host__ __device__ constexpr int fixed_bytes(int bn) {
-  return 2 * w_chunk(bn) + 2 * CHUNK_A + epi_warps(bn) * STG_BYTES + 1024 /* barriers */ + 1024 /* alignment */;
+// shared memory: X ring (ra chunks) | lo ring (2) | W (w_slots chunks: 2 when streamed, nkc when resident) |
+// epilogue transpose tiles | barriers; + 1 KB alignment slack
+__host__ __device__ constexpr int fixed_bytes(int bn, int w_slots) {
+  return w_slots * w_chunk(bn) + 2 * CHUNK_A + NE * STG_BYTES + 1024 /* barriers */ + 1024 /* alignment */;
 }
-__host__ __device__ constexpr int ring_a(int bn) { return (SMEM_MAX - fixed_bytes(bn)) / CHUNK_A; }
-__host__ __device__ constexpr int smem_bytes(int bn) { return fixed_bytes(bn) + ring_a(bn) * CHUNK_A; }
+__host__ __device__ constexpr int ring_a(int bn, int w_slots) {
+  return (SMEM_MAX - fixed_bytes(bn, w_slots)) / CHUNK_A < RA_MAX ? (SMEM_MAX - fixed_bytes(bn, w_slots)) / CHUNK_A : RA_MAX;
+}
 
 struct Params {
   const uint8_t* w_img;      // [ntiles][nkc] { hi[bn x 128 B] | lo[bn x 128 B] }, swizzled like the A chunk
@@ -68,6 +72,8 @@ struct Params {
   const float* bias;
   int64_t M; int N; int K;
   int nkc, ntiles;
+  int ra;                    // X chunks in flight (ring slots)
+  int groups;                // resident-W mode: CTAs per n-tile (CTA b works on n-tile b % ntiles, m-tiles b / ntiles + i * groups)
   int64_t mtiles;
   int epi;
   float scale;               // 1/(1-p) for DROPOUT and MASK (p quantised to 1/256)
@@ -138,40 +144,51 @@ __host__ __device__ __forceinline__ uint32_t drop_thresh(float p) {   // p quant
 namespace gcnb {
 namespace xs {
 
-template <int BN, int MODE>   // MODE 0: 3xTF32 (fp32 parity), 1: single-pass TF32
-__global__ void __launch_bounds__(threads_for(BN), 1)
+// WRES: the W chunks of the CTA's n-tile stay resident in shared memory for the whole kernel (loaded once);
+// otherwise they stream through a ring of 2 per k-chunk (large K).  With resident W a CTA keeps ONE n-tile
+// and the CTAs b, b+1, .. b+ntiles-1 walk the same m-tiles at the same time, so that an X chunk comes out of
+// HBM once and out of L2 for the others.
+template <int BN, int MODE, bool WRES>   // MODE 0: 3xTF32 (fp32 parity), 1: single-pass TF32
+__global__ void __launch_bounds__(THREADS, 1)
 xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
   extern __shared__ uint8_t smem_raw[];
-  constexpr int RA = ring_a(BN);                  // X chunks in flight
-  constexpr int NE = epi_warps(BN);               // epilogue warps
+  const int RA = p.ra;                            // X chunks in flight
   constexpr int NEG = NE / 4;                     // epilogue warps per TMEM lane quadrant
   constexpr int W_CHUNK = w_chunk(BN);
-  constexpr uint32_t W_BYTES = (MODE == 0 ? 2 : 1) * BN * 128;
   constexpr uint32_t IDESC = make_idesc(BN);
   constexpr int TMEM_COLS = 2 * BN;               // two accumulator buffers (128 / 256 columns)
-  static_assert(RA >= 2, "no room for the X ring");
+  const int w_slots = WRES ? p.nkc : 2;
   // 1024-byte alignment (of the shared-space address) for the 128-byte swizzle atoms
   uint8_t* smem = smem_raw + ((1024u - (smem_addr(smem_raw) & 1023u)) & 1023u);
   uint8_t* ring = smem;                            // RA x 16 KB raw X chunks
   uint8_t* lo = ring + RA * CHUNK_A;               // 2 x 16 KB low parts
-  uint8_t* wbuf = lo + 2 * CHUNK_A;                // 2 x W chunk
-  uint8_t* stg = wbuf + 2 * W_CHUNK;               // NE transpose tiles
+  uint8_t* wbuf = lo + 2 * CHUNK_A;                // W chunks
+  uint8_t* stg = wbuf + w_slots * W_CHUNK;         // NE transpose tiles
   uint64_t* bars = reinterpret_cast<uint64_t*>(stg + NE * STG_BYTES);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * RA + 12);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * RA_MAX + 12);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t bar0 = smem_addr(bars);
   auto FULLA = [&](int s) { return bar0 + 8u * (uint32_t)s; };
-  auto EMPTYA = [&](int s) { return bar0 + 8u * (uint32_t)(RA + s); };
-  auto FULLW = [&](int s) { return bar0 + 8u * (uint32_t)(2 * RA + s); };
-  auto EMPTYW = [&](int s) { return bar0 + 8u * (uint32_t)(2 * RA + 2 + s); };
-  auto CONV = [&](int s) { return bar0 + 8u * (uint32_t)(2 * RA + 4 + s); };
-  auto LOEMPTY = [&](int s) { return bar0 + 8u * (uint32_t)(2 * RA + 6 + s); };
-  auto TFULL = [&](int b) { return bar0 + 8u * (uint32_t)(2 * RA + 8 + b); };
-  auto TEMPTY = [&](int b) { return bar0 + 8u * (uint32_t)(2 * RA + 10 + b); };
+  auto EMPTYA = [&](int s) { return bar0 + 8u * (uint32_t)(RA_MAX + s); };
+  auto FULLW = [&](int s) { return bar0 + 8u * (uint32_t)(2 * RA_MAX + s); };
+  auto EMPTYW = [&](int s) { return bar0 + 8u * (uint32_t)(2 * RA_MAX + 2 + s); };
+  auto CONV = [&](int s) { return bar0 + 8u * (uint32_t)(2 * RA_MAX + 4 + s); };
+  auto LOEMPTY = [&](int s) { return bar0 + 8u * (uint32_t)(2 * RA_MAX + 6 + s); };
+  auto TFULL = [&](int b) { return bar0 + 8u * (uint32_t)(2 * RA_MAX + 8 + b); };
+  auto TEMPTY = [&](int b) { return bar0 + 8u * (uint32_t)(2 * RA_MAX + 10 + b); };
+  // work of this CTA: units u = u0, u0 + ustep, ... of (m-tile, n-tile) pairs
+  //   streamed W: unit index t over all pairs, n-tile fastest;   resident W: fixed n-tile, m-tiles of its group
+  const int64_t n_tiles = p.mtiles * p.ntiles;
+  const int my_nt = WRES ? (int)(blockIdx.x % p.ntiles) : 0;
+  const int64_t u0 = WRES ? (int64_t)(blockIdx.x / p.ntiles) : (int64_t)blockIdx.x;
+  const int64_t ustep = WRES ? (int64_t)p.groups : (int64_t)gridDim.x;
+  const int64_t uend = WRES ? p.mtiles : n_tiles;
+  auto unit_nt = [&](int64_t u) { return WRES ? my_nt : (int)(u % p.ntiles); };
+  auto unit_m0 = [&](int64_t u) { return (WRES ? u : u / p.ntiles) * BM; };
 
   if (tid == 0) {
-    for (int s = 0; s < RA; ++s) {
+    for (int s = 0; s < RA_MAX; ++s) {
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(FULLA(s)));
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(EMPTYA(s)));
     }
@@ -195,14 +212,12 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = *tmem_slot;
 
-  const int64_t n_tiles = p.mtiles * p.ntiles;     // n-tile fastest: the CTAs sharing an X tile run together
-
   if (warp == 0) {
     // ---------------- X producer ----------------
     if (lane == 0) {
       uint32_t it = 0;
-      for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-        const int64_t m0 = (t / p.ntiles) * BM;
+      for (int64_t t = u0; t < uend; t += ustep) {
+        const int64_t m0 = unit_m0(t);
         for (int kc = 0; kc < p.nkc; ++kc, ++it) {
           const int s = it % RA;
           mbar_wait(EMPTYA(s), ((it / RA) & 1) ^ 1);
@@ -217,17 +232,29 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
   } else if (warp == 2) {
     // ---------------- W producer ----------------
     if (lane == 0) {
-      uint32_t it = 0;
-      for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-        const int nt = (int)(t % p.ntiles);
-        for (int kc = 0; kc < p.nkc; ++kc, ++it) {
-          const int s = it & 1;
-          mbar_wait(EMPTYW(s), ((it >> 1) & 1) ^ 1);
-          const uint32_t full = FULLW(s);
-          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(full), "r"(W_BYTES) : "memory");
-          const uint8_t* src_w = p.w_img + ((int64_t)nt * p.nkc + kc) * W_CHUNK;
-          asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                       ::"r"(smem_addr(wbuf + s * W_CHUNK)), "l"(src_w), "r"(W_BYTES), "r"(full) : "memory");
+      if constexpr (WRES) {
+        if (u0 < uend) {   // every chunk of this CTA's n-tile, once
+          const uint32_t full = FULLW(0);
+          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(full), "r"((uint32_t)(p.nkc * W_CHUNK)) : "memory");
+          for (int kc = 0; kc < p.nkc; ++kc) {
+            const uint8_t* src_w = p.w_img + ((int64_t)my_nt * p.nkc + kc) * W_CHUNK;
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(smem_addr(wbuf + kc * W_CHUNK)), "l"(src_w), "r"((uint32_t)W_CHUNK), "r"(full) : "memory");
+          }
+        }
+      } else {
+        uint32_t it = 0;
+        for (int64_t t = u0; t < uend; t += ustep) {
+          const int nt = unit_nt(t);
+          for (int kc = 0; kc < p.nkc; ++kc, ++it) {
+            const int s = it & 1;
+            mbar_wait(EMPTYW(s), ((it >> 1) & 1) ^ 1);
+            const uint32_t full = FULLW(s);
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(full), "r"((uint32_t)W_CHUNK) : "memory");
+            const uint8_t* src_w = p.w_img + ((int64_t)nt * p.nkc + kc) * W_CHUNK;
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(smem_addr(wbuf + s * W_CHUNK)), "l"(src_w), "r"((uint32_t)W_CHUNK), "r"(full) : "memory");
+          }
         }
       }
     }
@@ -235,7 +262,10 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
     // ---------------- MMA issuer ----------------
     if (lane == 0) {
       uint32_t it = 0, tl = 0;
-      for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++tl) {
+      if constexpr (WRES) {
+        if (u0 < uend) mbar_wait(FULLW(0), 0);
+      }
+      for (int64_t t = u0; t < uend; t += ustep, ++tl) {
         const uint32_t buf = tl & 1;
         mbar_wait(TEMPTY(buf), ((tl >> 1) & 1) ^ 1);       // the epilogue has drained this accumulator
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -243,11 +273,11 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
         for (int kc = 0; kc < p.nkc; ++kc, ++it) {
           const int sa = it % RA, sw = it & 1;
           mbar_wait(FULLA(sa), (it / RA) & 1);
-          mbar_wait(FULLW(sw), (it >> 1) & 1);
+          if constexpr (!WRES) mbar_wait(FULLW(sw), (it >> 1) & 1);
           if constexpr (MODE == 0) mbar_wait(CONV(sw), (it >> 1) & 1);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           const uint32_t a_raw = smem_addr(ring + sa * CHUNK_A), a_lo = smem_addr(lo + sw * CHUNK_A);
-          const uint32_t w_hi = smem_addr(wbuf + sw * W_CHUNK), w_lo = w_hi + BN * 128;
+          const uint32_t w_hi = smem_addr(wbuf + (WRES ? kc : sw) * W_CHUNK), w_lo = w_hi + BN * 128;
 #pragma unroll
           for (int ks = 0; ks < KC / 8; ++ks) {     // K = 8 tf32 = 32 bytes per MMA: advance inside the swizzle row
             const uint32_t o = ks * 32;
@@ -259,7 +289,7 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
             }
           }
           commit(EMPTYA(sa));                        // ring slots reusable once these MMAs have read them
-          commit(EMPTYW(sw));
+          if constexpr (!WRES) commit(EMPTYW(sw));
           if constexpr (MODE == 0) commit(LOEMPTY(sw));
         }
         commit(TFULL(buf));                          // accumulator complete
@@ -270,7 +300,7 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
     if constexpr (MODE == 0) {
       const int ct = tid - 128;                      // 0..127
       uint32_t it = 0;
-      for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+      for (int64_t t = u0; t < uend; t += ustep) {
         for (int kc = 0; kc < p.nkc; ++kc, ++it) {
           const int sa = it % RA, sw = it & 1;
           mbar_wait(FULLA(sa), (it / RA) & 1);
@@ -304,10 +334,10 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
     uint8_t* my = stg + (warp - 8) * STG_BYTES;
     const int64_t n4 = (p.N + 3) / 4;                // dropout hash groups per row
     uint32_t tl = 0;
-    for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++tl) {
+    for (int64_t t = u0; t < uend; t += ustep, ++tl) {
       const uint32_t buf = tl & 1;
-      const int nt = (int)(t % p.ntiles);
-      const int64_t m0 = (t / p.ntiles) * BM + q * 32;
+      const int nt = unit_nt(t);
+      const int64_t m0 = unit_m0(t) + q * 32;
       const int n0 = nt * BN;
       const int64_t myrow = m0 + lane;
       mbar_wait(TFULL(buf), (tl >> 1) & 1);
@@ -446,20 +476,26 @@ static EncodeTiledFn encode_tiled() {
   return f;
 }
 
-template <int BN, int MODE>
-static int xs_launch(const CUtensorMap& tmap, const xs::Params& p, int grid, cudaStream_t stream) {
+template <int BN, int MODE, bool WRES>
+static int xs_launch(const CUtensorMap& tmap, const xs::Params& p, int grid, int smem, cudaStream_t stream) {
   static std::atomic<uint64_t> configured{0};   // per-device opt-in to > 48 KB of dynamic shared memory
   int dev = 0;
   GCNB_CHECK_CUDA(cudaGetDevice(&dev));
   const uint64_t bit = 1ull << (dev & 63);
   if (dev >= 64 || !(configured.load(std::memory_order_relaxed) & bit)) {
-    GCNB_CHECK_CUDA(cudaFuncSetAttribute(xs::xs_kernel<BN, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         xs::smem_bytes(BN)));
+    GCNB_CHECK_CUDA(cudaFuncSetAttribute(xs::xs_kernel<BN, MODE, WRES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         xs::SMEM_MAX));
     configured.fetch_or(bit, std::memory_order_relaxed);
   }
-  xs::xs_kernel<BN, MODE><<<grid, xs::threads_for(BN), xs::smem_bytes(BN), stream>>>(tmap, p);
+  xs::xs_kernel<BN, MODE, WRES><<<grid, xs::THREADS, smem, stream>>>(tmap, p);
   GCNB_CHECK_CUDA(cudaGetLastError());
   return GCNB_OK;
+}
+
+template <int MODE>
+static int xs_dispatch(int bn, bool wres, const CUtensorMap& tmap, const xs::Params& p, int grid, int smem, cudaStream_t stream) {
+  if (bn == 64) return wres ? xs_launch<64, MODE, true>(tmap, p, grid, smem, stream) : xs_launch<64, MODE, false>(tmap, p, grid, smem, stream);
+  return wres ? xs_launch<128, MODE, true>(tmap, p, grid, smem, stream) : xs_launch<128, MODE, false>(tmap, p, grid, smem, stream);
 }
 
 // Returns GCNB_OK when the product ran here, 1 when the shape is not this kernel's (caller falls back).
@@ -467,13 +503,27 @@ int xw_stream_run(const float* X, int64_t ldx, const float* W, int64_t ldw, int 
                   int64_t M, int N, int K, const float* bias, int epi, const uint32_t* mask_in, uint32_t* mask_out,
                   int64_t ldm, float drop_p, uint32_t seed, int precision, int n_sm, cudaStream_t stream) {
   static const int enabled = getenv("GCNB_XW_STREAM") ? atoi(getenv("GCNB_XW_STREAM")) : 1;
+  // GCNB_XW_WRES: 1 (default) keeps the W chunks of a CTA's n-tile resident when they fit 64 KB, 0 always streams them
+  static const int wres_ok = getenv("GCNB_XW_WRES") ? atoi(getenv("GCNB_XW_WRES")) : 1;
   if (!enabled || precision > 1 || M < 1024 || K < 1 || K > 4096 || N < 1) return 1;
   if (((uintptr_t)X & 15) || (ldx % 4) != 0 || M >= ((int64_t)1 << 31)) return 1;
   EncodeTiledFn enc = encode_tiled();
   if (!enc) return 1;
-  const int bn = N <= 64 ? 64 : 128;
-  const int ntiles = (N + bn - 1) / bn;
   const int nkc = (K + xs::KC - 1) / xs::KC;
+  // tile width and W placement: resident W (<= 64 KB: all k-chunks of one n-tile) with the widest tile that
+  // allows it, else streamed W chunks
+  int bn = N <= 64 ? 64 : 128;
+  bool wres = false;
+  if (wres_ok) {
+    if (N > 64 && nkc * xs::w_chunk(128) <= 65536) { bn = 128; wres = true; }
+    else if (nkc * xs::w_chunk(64) <= 65536) { bn = 64; wres = true; }
+  }
+  int ntiles = (N + bn - 1) / bn;
+  if (wres && ntiles > n_sm) { wres = false; bn = N <= 64 ? 64 : 128; ntiles = (N + bn - 1) / bn; }
+  const int w_slots = wres ? nkc : 2;
+  const int ra = xs::ring_a(bn, w_slots);
+  if (ra < 2) return 1;
+  const int smem = xs::fixed_bytes(bn, w_slots) + ra * xs::CHUNK_A;
   CUtensorMap tmap;
   const cuuint64_t gdim[2] = {(cuuint64_t)K, (cuuint64_t)M};
   const cuuint64_t gstride[1] = {(cuuint64_t)ldx * 4};
@@ -493,16 +543,22 @@ int xw_stream_run(const float* X, int64_t ldx, const float* W, int64_t ldw, int 
   xs::Params p;
   p.w_img = img; p.D = D; p.ldd = ldd; p.mask_in = mask_in; p.mask_out = mask_out; p.ldm = ldm; p.bias = bias;
   p.M = M; p.N = N; p.K = K; p.nkc = nkc; p.ntiles = ntiles; p.mtiles = (M + xs::BM - 1) / xs::BM;
+  p.ra = ra;
   p.epi = epi;
   p.keep_thresh = xs::drop_thresh(drop_p);
   p.scale = (epi & (GCNB_EPI_DROPOUT | GCNB_EPI_MASK)) ? 256.f / (256.f - (float)p.keep_thresh) : 1.f;
   p.seed = seed;
   p.d_vec = (((uintptr_t)D & 15) == 0) && (ldd % 4 == 0) && (N % 4 == 0);
-  const int64_t tiles = p.mtiles * ntiles;
-  const int grid = (int)std::min<int64_t>(tiles, n_sm);
-  int rc;
-  if (precision == 0) rc = bn == 64 ? xs_launch<64, 0>(tmap, p, grid, stream) : xs_launch<128, 0>(tmap, p, grid, stream);
-  else rc = bn == 64 ? xs_launch<64, 1>(tmap, p, grid, stream) : xs_launch<128, 1>(tmap, p, grid, stream);
+  int grid;
+  if (wres) {
+    p.groups = (int)std::max<int64_t>(1, std::min<int64_t>(p.mtiles, n_sm / ntiles));
+    grid = p.groups * ntiles;
+  } else {
+    p.groups = 0;
+    grid = (int)std::min<int64_t>(p.mtiles * ntiles, n_sm);
+  }
+  const int rc = precision == 0 ? xs_dispatch<0>(bn, wres, tmap, p, grid, smem, stream)
+                                : xs_dispatch<1>(bn, wres, tmap, p, grid, smem, stream);
   cudaFreeAsync(img, stream);
   return rc;
 }

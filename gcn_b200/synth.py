@@ -124,6 +124,21 @@ def edges_rmat(scale, edge_factor, device, abcd=(0.57, 0.19, 0.19, 0.05), seed=S
     return torch.cat(srcs), torch.cat(dsts)
 
 
+def _unique_sorted(key, n):
+    """torch.unique(key) (sorted), in row-range pieces when key has 2^31 or more elements (the CUB sort behind
+    torch.unique takes at most 2^31 - 1: R-MAT scale 24 with edge factor 64 has 2.16 G keys)."""
+    if key.numel() < 2 ** 31 - 1:
+        return torch.unique(key)
+    pieces = int(key.numel() // (2 ** 30)) + 1
+    parts = []
+    for i in range(pieces):
+        lo, hi = (n * i) // pieces, (n * (i + 1)) // pieces
+        sel = key[(key >= lo * n) & (key < hi * n)]
+        parts.append(torch.unique(sel))
+        del sel
+    return torch.cat(parts)
+
+
 def normalized_csr(src, dst, n, to_host=True):
     """Symmetrise, drop duplicates and the diagonal, add I, scale by D^-½ on both sides.
     Returns (rowptr int32, col int32, val fp32) as numpy arrays (or device tensors)."""
@@ -133,19 +148,27 @@ def normalized_csr(src, dst, n, to_host=True):
     src, dst = src[keep], dst[keep]
     key = torch.cat((src * n + dst, dst * n + src, diag * n + diag))
     del src, dst, keep
-    key = torch.unique(key)  # sorted: row-major, ascending columns
-    if key.numel() >= 2 ** 31 - 16:
-        raise ValueError(f"{key.numel()} non-zeros do not fit the int32 CSR offsets of one plan "
+    key = _unique_sorted(key, n)  # sorted: row-major, ascending columns
+    nnz = key.numel()
+    if nnz >= 2 ** 31 - 16:
+        raise ValueError(f"{nnz} non-zeros do not fit the int32 CSR offsets of one plan "
                          "(include/gcn_b200.h: nnz < 2^31 - 16); partition the rows first")
-    row = torch.div(key, n, rounding_mode="floor")
-    col = key - row * n
-    del key
-    counts = torch.bincount(row, minlength=n)
-    rowptr = torch.zeros(n + 1, dtype=torch.int64, device=dev)
-    torch.cumsum(counts, 0, out=rowptr[1:])
+    # row pointers by binary search of the row boundaries in the sorted keys (no 2^31 limits, no histogram)
+    rowptr = torch.searchsorted(key, diag * n)
+    rowptr = torch.cat((rowptr, torch.tensor([nnz], device=dev, dtype=rowptr.dtype)))
+    counts = rowptr[1:] - rowptr[:-1]
     dinv = counts.to(torch.float64).pow_(-0.5)   # row sum of (A + I) with unit weights = its nnz
-    val = (dinv[row] * dinv[col]).to(torch.float32)
-    rowptr, col = rowptr.to(torch.int32), col.to(torch.int32)
+    col = torch.empty(nnz, dtype=torch.int32, device=dev)
+    val = torch.empty(nnz, dtype=torch.float32, device=dev)
+    step = 1 << 28
+    for z0 in range(0, nnz, step):               # in pieces: the fp64 temporaries of 2 G non-zeros would take 50 GB
+        k = key[z0:z0 + step]
+        r = torch.div(k, n, rounding_mode="floor")
+        c = k - r * n
+        col[z0:z0 + step] = c.to(torch.int32)
+        val[z0:z0 + step] = (dinv[r] * dinv[c]).to(torch.float32)
+    del key
+    rowptr = rowptr.to(torch.int32)
     if not to_host:
         return rowptr, col, val
     return rowptr.cpu().numpy(), col.cpu().numpy(), val.cpu().numpy()

@@ -54,7 +54,7 @@ extern "C" {
 #define GCNB_PLAN_ASSUME_SYMMETRIC 1 /* skip the check; A^T·dY runs on A (reference behaviour, gcn6.py:50-62) */
 #define GCNB_PLAN_NO_TRANSPOSE 2     /* never build A^T (forward-only plans) */
 #define GCNB_PLAN_PANEL 4            /* always build the panel class (32-row panels walking their columns in step) */
-#define GCNB_PLAN_NO_PANEL 8         /* never build it; default: built when nnz >= 96 m and the panels share columns */
+#define GCNB_PLAN_NO_PANEL 8         /* never build it (the default unless GCNB_PANEL is set in the environment) */
 
 typedef struct gcnb_plan gcnb_plan_t;
 
