@@ -8,17 +8,17 @@
 // every fp32 value converted to tf32 hi/lo by the same threads that wait for it, a CTA-wide barrier per
 // k-block, per-thread row stores) ran at ~27 % of the HBM time of these shapes.
 // Here one CTA per SM loops over its 128-row tiles, with fixed warp roles and separate rings per stream:
-//   warp 0      X producer: one TMA tensor-map load per k-chunk (128 rows x 32 floats, SWIZZLE_128B, rows
-//               past M and columns past K zero-filled by the TMA unit) into a DEEP ring — the X chunks are
-//               the only HBM reads of the kernel, and ~100 KB of them must be in flight per SM to cover
-//               the HBM latency (the first version of this kernel staged X, lo(X) and W together, had
-//               32-64 KB of X in flight and ran at 16 B/clk/SM, profiles/r02_d_launches_epoch_products.csv)
-//   warp 2      W producer: bulk copies of the prepared W chunk (hi | lo images, L2-resident) into a ring of 2
+//   warp 0      X producer: one TMA tensor-map load per k-chunk (128 rows x 32 floats, SWIZZLE_128B, rows past M
+//               and columns past K zero-filled by the TMA unit) into a deep ring.  Measured on the way here:
+//               staging X, lo(X) and W in one ring leaves 32-64 KB of X in flight (profiles/r02_d_*); 16-byte
+//               cp.async copies by four loader warps instead of the TMA load are slower (r02_k_xw_shapes.jsonl)
+//   warp 2      W producer: TMA bulk copies of the prepared W chunks (hi | lo images, L2-resident), once per CTA
+//               when they fit 64 KB, else through a ring of 2
 //   warp 1      MMA issuer (one elected thread): tcgen05.mma kind::tf32, A and B from shared memory,
 //               accumulator in TMEM, two accumulator buffers so the epilogue of tile i overlaps the MMAs of
 //               tile i+1; tcgen05.commit frees the rings / publishes the accumulator
 //   warps 4-7   converters: only the LOW part of the 3xTF32 split is computed, lo = tf32(x - trunc13(x)),
-//               into a ring of 2; the HIGH part is the raw fp32 word with its 13 low mantissa bits cleared
+//               into a small ring; the HIGH part is the raw fp32 word with its 13 low mantissa bits cleared
 //   warps 8-15  epilogue (8-11 when BN = 64): tcgen05.ld, bias / ReLU / dropout / mask with thread = row,
 //               one 32-bit word of mask bits per 32 outputs, then a transpose through a private
 //               shared-memory tile so that every store instruction writes full 128-byte lines
@@ -56,11 +56,13 @@ constexpr int RA_MAX = 12;       // most X chunks in flight (barrier slots)
 __host__ __device__ constexpr int w_chunk(int bn) { return 2 * bn * 128; }      // hi | lo
 // shared memory: X ring (ra chunks) | lo ring (2) | W (w_slots chunks: 2 when streamed, nkc when resident) |
 // epilogue transpose tiles | barriers; + 1 KB alignment slack
-__host__ __device__ constexpr int fixed_bytes(int bn, int w_slots) {
-  return w_slots * w_chunk(bn) + 2 * CHUNK_A + NE * STG_BYTES + 1024 /* barriers */ + 1024 /* alignment */;
+constexpr int LO_MAX = 4;        // most low-part chunks in flight
+__host__ __device__ constexpr int fixed_bytes(int bn, int w_slots, int lo_slots) {
+  return w_slots * w_chunk(bn) + lo_slots * CHUNK_A + NE * STG_BYTES + 1024 /* barriers */ + 1024 /* alignment */;
 }
-__host__ __device__ constexpr int ring_a(int bn, int w_slots) {
-  return (SMEM_MAX - fixed_bytes(bn, w_slots)) / CHUNK_A < RA_MAX ? (SMEM_MAX - fixed_bytes(bn, w_slots)) / CHUNK_A : RA_MAX;
+__host__ __device__ constexpr int ring_a(int bn, int w_slots, int lo_slots) {
+  return (SMEM_MAX - fixed_bytes(bn, w_slots, lo_slots)) / CHUNK_A < RA_MAX
+             ? (SMEM_MAX - fixed_bytes(bn, w_slots, lo_slots)) / CHUNK_A : RA_MAX;
 }
 
 struct Params {
@@ -73,6 +75,7 @@ struct Params {
   int64_t M; int N; int K;
   int nkc, ntiles;
   int ra;                    // X chunks in flight (ring slots)
+  int lo;                    // low-part chunks in flight (2..LO_MAX)
   int groups;                // resident-W mode: CTAs per n-tile (CTA b works on n-tile b % ntiles, m-tiles b / ntiles + i * groups)
   int64_t mtiles;
   int epi;
@@ -162,10 +165,11 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
   uint8_t* smem = smem_raw + ((1024u - (smem_addr(smem_raw) & 1023u)) & 1023u);
   uint8_t* ring = smem;                            // RA x 16 KB raw X chunks
   uint8_t* lo = ring + RA * CHUNK_A;               // 2 x 16 KB low parts
-  uint8_t* wbuf = lo + 2 * CHUNK_A;                // W chunks
+  const int LO = p.lo;
+  uint8_t* wbuf = lo + LO * CHUNK_A;               // W chunks
   uint8_t* stg = wbuf + w_slots * W_CHUNK;         // NE transpose tiles
   uint64_t* bars = reinterpret_cast<uint64_t*>(stg + NE * STG_BYTES);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * RA_MAX + 12);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * RA_MAX + 8 + 2 * LO_MAX);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t bar0 = smem_addr(bars);
@@ -173,10 +177,10 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
   auto EMPTYA = [&](int s) { return bar0 + 8u * (uint32_t)(RA_MAX + s); };
   auto FULLW = [&](int s) { return bar0 + 8u * (uint32_t)(2 * RA_MAX + s); };
   auto EMPTYW = [&](int s) { return bar0 + 8u * (uint32_t)(2 * RA_MAX + 2 + s); };
-  auto CONV = [&](int s) { return bar0 + 8u * (uint32_t)(2 * RA_MAX + 4 + s); };
-  auto LOEMPTY = [&](int s) { return bar0 + 8u * (uint32_t)(2 * RA_MAX + 6 + s); };
-  auto TFULL = [&](int b) { return bar0 + 8u * (uint32_t)(2 * RA_MAX + 8 + b); };
-  auto TEMPTY = [&](int b) { return bar0 + 8u * (uint32_t)(2 * RA_MAX + 10 + b); };
+  auto TFULL = [&](int b) { return bar0 + 8u * (uint32_t)(2 * RA_MAX + 4 + b); };
+  auto TEMPTY = [&](int b) { return bar0 + 8u * (uint32_t)(2 * RA_MAX + 6 + b); };
+  auto CONV = [&](int s) { return bar0 + 8u * (uint32_t)(2 * RA_MAX + 8 + s); };
+  auto LOEMPTY = [&](int s) { return bar0 + 8u * (uint32_t)(2 * RA_MAX + 8 + LO_MAX + s); };
   // work of this CTA: units u = u0, u0 + ustep, ... of (m-tile, n-tile) pairs
   //   streamed W: unit index t over all pairs, n-tile fastest;   resident W: fixed n-tile, m-tiles of its group
   const int64_t n_tiles = p.mtiles * p.ntiles;
@@ -192,11 +196,13 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(FULLA(s)));
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(EMPTYA(s)));
     }
+    for (int b = 0; b < LO_MAX; ++b) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 128;" ::"r"(CONV(b)));
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(LOEMPTY(b)));
+    }
     for (int b = 0; b < 2; ++b) {
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(FULLW(b)));
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(EMPTYW(b)));
-      asm volatile("mbarrier.init.shared::cta.b64 [%0], 128;" ::"r"(CONV(b)));
-      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(LOEMPTY(b)));
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(TFULL(b)));
       asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(TEMPTY(b)), "r"(NE * 32));
     }
@@ -213,7 +219,9 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ---------------- X producer ----------------
+    // ---------------- X producer: one TMA tensor-map load per k-chunk ----------------
+    // (16-byte cp.async copies by four loader warps into the same layout were tried instead — no tensor map, any
+    // leading dimension — and were slower: layer-1 product 2.72 vs 2.43 ms, profiles/r02_k_xw_shapes.jsonl.)
     if (lane == 0) {
       uint32_t it = 0;
       for (int64_t t = u0; t < uend; t += ustep) {
@@ -271,12 +279,12 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const uint32_t tmem_d = tmem_base + buf * BN;
         for (int kc = 0; kc < p.nkc; ++kc, ++it) {
-          const int sa = it % RA, sw = it & 1;
+          const int sa = it % RA, sw = it & 1, sl = it % LO;
           mbar_wait(FULLA(sa), (it / RA) & 1);
           if constexpr (!WRES) mbar_wait(FULLW(sw), (it >> 1) & 1);
-          if constexpr (MODE == 0) mbar_wait(CONV(sw), (it >> 1) & 1);
+          mbar_wait(CONV(sl), (it / LO) & 1);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-          const uint32_t a_raw = smem_addr(ring + sa * CHUNK_A), a_lo = smem_addr(lo + sw * CHUNK_A);
+          const uint32_t a_raw = smem_addr(ring + sa * CHUNK_A), a_lo = smem_addr(lo + sl * CHUNK_A);
           const uint32_t w_hi = smem_addr(wbuf + (WRES ? kc : sw) * W_CHUNK), w_lo = w_hi + BN * 128;
 #pragma unroll
           for (int ks = 0; ks < KC / 8; ++ks) {     // K = 8 tf32 = 32 bytes per MMA: advance inside the swizzle row
@@ -290,40 +298,43 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
           }
           commit(EMPTYA(sa));                        // ring slots reusable once these MMAs have read them
           if constexpr (!WRES) commit(EMPTYW(sw));
-          if constexpr (MODE == 0) commit(LOEMPTY(sw));
+          commit(LOEMPTY(sl));
         }
         commit(TFULL(buf));                          // accumulator complete
       }
     }
   } else if (warp >= 4 && warp < 8) {
     // ---------------- converters: lo = tf32(x - trunc13(x)) on the physical (swizzled) layout ----------------
-    if constexpr (MODE == 0) {
+    // The high part is written back truncated, so that it does not matter whether the tensor core truncates or
+    // rounds the 13 low mantissa bits of an fp32 word it is handed as tf32 (fence.proxy.async publishes the generic
+    // stores to the tensor core's proxy).  Single-pass mode: the same without the low part.
+    {
       const int ct = tid - 128;                      // 0..127
       uint32_t it = 0;
       for (int64_t t = u0; t < uend; t += ustep) {
         for (int kc = 0; kc < p.nkc; ++kc, ++it) {
-          const int sa = it % RA, sw = it & 1;
+          const int sa = it % RA, sl = it % LO;
           mbar_wait(FULLA(sa), (it / RA) & 1);
-          mbar_wait(LOEMPTY(sw), ((it >> 1) & 1) ^ 1);
+          mbar_wait(LOEMPTY(sl), ((it / LO) & 1) ^ 1);
           uint8_t* raw = ring + sa * CHUNK_A;
-          uint8_t* lop = lo + sw * CHUNK_A;
+          uint8_t* lop = lo + sl * CHUNK_A;
 #pragma unroll
           for (int j = 0; j < CHUNK_A / 16 / 128; ++j) {
             const int off = (ct + j * 128) * 16;
             const uint4 v = *reinterpret_cast<const uint4*>(raw + off);
-            uint4 o;
-            o.x = to_tf32(__uint_as_float(v.x) - __uint_as_float(v.x & 0xffffe000u));
-            o.y = to_tf32(__uint_as_float(v.y) - __uint_as_float(v.y & 0xffffe000u));
-            o.z = to_tf32(__uint_as_float(v.z) - __uint_as_float(v.z & 0xffffe000u));
-            o.w = to_tf32(__uint_as_float(v.w) - __uint_as_float(v.w & 0xffffe000u));
-            *reinterpret_cast<uint4*>(lop + off) = o;
-            // the high part is written back truncated, so that it does not matter whether the tensor core
-            // truncates or rounds the 13 low mantissa bits of an fp32 word it is handed as tf32
+            if constexpr (MODE == 0) {
+              uint4 o;
+              o.x = to_tf32(__uint_as_float(v.x) - __uint_as_float(v.x & 0xffffe000u));
+              o.y = to_tf32(__uint_as_float(v.y) - __uint_as_float(v.y & 0xffffe000u));
+              o.z = to_tf32(__uint_as_float(v.z) - __uint_as_float(v.z & 0xffffe000u));
+              o.w = to_tf32(__uint_as_float(v.w) - __uint_as_float(v.w & 0xffffe000u));
+              *reinterpret_cast<uint4*>(lop + off) = o;
+            }
             *reinterpret_cast<uint4*>(raw + off) =
                 make_uint4(v.x & 0xffffe000u, v.y & 0xffffe000u, v.z & 0xffffe000u, v.w & 0xffffe000u);
           }
           asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic stores -> tensor core's proxy
-          mbar_arrive(CONV(sw));
+          mbar_arrive(CONV(sl));
         }
       }
     }
@@ -507,8 +518,6 @@ int xw_stream_run(const float* X, int64_t ldx, const float* W, int64_t ldw, int 
   static const int wres_ok = getenv("GCNB_XW_WRES") ? atoi(getenv("GCNB_XW_WRES")) : 1;
   if (!enabled || precision > 1 || M < 1024 || K < 1 || K > 4096 || N < 1) return 1;
   if (((uintptr_t)X & 15) || (ldx % 4) != 0 || M >= ((int64_t)1 << 31)) return 1;
-  EncodeTiledFn enc = encode_tiled();
-  if (!enc) return 1;
   const int nkc = (K + xs::KC - 1) / xs::KC;
   // tile width and W placement: resident W (<= 64 KB: all k-chunks of one n-tile) with the widest tile that
   // allows it, else streamed W chunks
@@ -521,9 +530,15 @@ int xw_stream_run(const float* X, int64_t ldx, const float* W, int64_t ldw, int 
   int ntiles = (N + bn - 1) / bn;
   if (wres && ntiles > n_sm) { wres = false; bn = N <= 64 ? 64 : 128; ntiles = (N + bn - 1) / bn; }
   const int w_slots = wres ? nkc : 2;
-  const int ra = xs::ring_a(bn, w_slots);
+  // ring depths: GCNB_XS_LO low-part chunks (2..4, default 2), the rest of shared memory is the X ring (GCNB_XS_RA caps it)
+  static const int lo_env = getenv("GCNB_XS_LO") ? atoi(getenv("GCNB_XS_LO")) : 2;
+  static const int ra_env = getenv("GCNB_XS_RA") ? atoi(getenv("GCNB_XS_RA")) : xs::RA_MAX;
+  const int lo_slots = std::max(2, std::min(xs::LO_MAX, lo_env));
+  const int ra = std::min(std::max(2, ra_env), xs::ring_a(bn, w_slots, lo_slots));
   if (ra < 2) return 1;
-  const int smem = xs::fixed_bytes(bn, w_slots) + ra * xs::CHUNK_A;
+  const int smem = xs::fixed_bytes(bn, w_slots, lo_slots) + ra * xs::CHUNK_A;
+  EncodeTiledFn enc = encode_tiled();
+  if (!enc) return 1;
   CUtensorMap tmap;
   const cuuint64_t gdim[2] = {(cuuint64_t)K, (cuuint64_t)M};
   const cuuint64_t gstride[1] = {(cuuint64_t)ldx * 4};
@@ -543,7 +558,7 @@ int xw_stream_run(const float* X, int64_t ldx, const float* W, int64_t ldw, int 
   xs::Params p;
   p.w_img = img; p.D = D; p.ldd = ldd; p.mask_in = mask_in; p.mask_out = mask_out; p.ldm = ldm; p.bias = bias;
   p.M = M; p.N = N; p.K = K; p.nkc = nkc; p.ntiles = ntiles; p.mtiles = (M + xs::BM - 1) / xs::BM;
-  p.ra = ra;
+  p.ra = ra; p.lo = lo_slots;
   p.epi = epi;
   p.keep_thresh = xs::drop_thresh(drop_p);
   p.scale = (epi & (GCNB_EPI_DROPOUT | GCNB_EPI_MASK)) ? 256.f / (256.f - (float)p.keep_thresh) : 1.f;

@@ -516,6 +516,9 @@ namespace gcnb {
 int xw_stream_run(const float* X, int64_t ldx, const float* W, int64_t ldw, int trans_w, float* D, int64_t ldd,
                   int64_t M, int N, int K, const float* bias, int epi, const uint32_t* mask_in, uint32_t* mask_out,
                   int64_t ldm, float drop_p, uint32_t seed, int precision, int n_sm, cudaStream_t stream);   // xw_stream.cu
+int xw_tallk_stream_run(const float* X, int64_t ldx, const float* W, int64_t ldw, float* D, int64_t ldd, int64_t M,
+                        int N, int64_t K, const float* bias, int epi, int precision, int n_sm,
+                        cudaStream_t stream);                                                              // xw_tallk_stream.cu
 // elementwise tail of gcnb_xw_ex for the products that do not run on the streaming kernel: one thread per
 // (row, 32-column word of the bit masks); same dropout hash (one word per 4 columns, one byte per element)
 __global__ void __launch_bounds__(256)
@@ -603,6 +606,12 @@ extern "C" int gcnb_xw_ex(const float* X, int64_t ldx, int trans_x, const float*
     const int r = xw_stream_run(X, ldx, W, ldw, trans_w, D, ldd, M, N, K, bias, epilogue_ex, mask_in, mask_out, ldm,
                                 drop_p, seed, precision, sm_count(dev), stream);
     if (r != 1) return r;   // ran (or failed) there; 1 = not that kernel's shape
+  }
+
+  if (K > 0 && trans_x && !trans_w) {   // dW = X^T·G with both operands row-major over the vertices
+    const int r = xw_tallk_stream_run(X, ldx, W, ldw, D, ldd, M, N, K, bias, epilogue, precision, sm_count(dev), stream);
+    if (r == GCNB_OK) return run_tail();
+    if (r != 1) return r;
   }
 
   if (K == 0) {   // empty sum: D = epilogue(0)

@@ -188,3 +188,39 @@ def test_mlp2_block_matches_unfused_autograd(p):
     # eval mode: no dropout
     s_eval = gemm.mlp2(X, W1, b1, W2, p=p, seed=seed, training=False)
     assert rel(s_eval.detach(), (torch.relu(X.double() @ W1r + b1r) @ W2r).detach()) < 1e-5
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two visible GPUs")
+def test_xw_on_second_device_after_first():
+    """The > 48 KB shared-memory opt-in of the tensor-core kernels is a per-device function attribute:
+    every kernel family on cuda:0 first, then on cuda:1, in one process."""
+    for dev in ("cuda:0", "cuda:1"):
+        g = torch.Generator(device=dev).manual_seed(4)
+        for (M, N, K, ta) in [(300, 40, 100, False), (2048, 96, 64, False), (5000, 200, 36, False),
+                              (64, 48, 6000, True), (100, 256, 8192, True)]:
+            X = torch.randn(K, M, device=dev, generator=g) if ta else torch.randn(M, K, device=dev, generator=g)
+            W = torch.randn(K, N, device=dev, generator=g) / K ** 0.5
+            ref = (X.double().t() if ta else X.double()) @ W.double()
+            assert rel(gemm.gemm_raw(X, W, trans_a=ta), ref) < 1e-5, (dev, M, N, K, ta)
+
+
+@pytest.mark.parametrize("K,M,N", [(400_000, 100, 256), (300_000, 256, 48), (70_001, 128, 128), (5_000, 4, 8),
+                                   (123_457, 48, 200)])
+@pytest.mark.parametrize("precision", [0, 1])
+def test_xw_tall_k_streaming_kernel(K, M, N, precision):
+    """dW = Xᵀ·G on the MN-major streaming kernel (xw_tallk_stream.cu): several accumulation chains per CTA
+    (K / 148 / 16 > 64 stages), the transposed route for M > 128, ragged K, padded leading dimensions; against
+    fp64 and against the first kernel's tall-K variant."""
+    g = torch.Generator(device=DEV).manual_seed(K % 1000 + M + N)
+    X = torch.randn(K, M, device=DEV, generator=g)
+    G = torch.randn(K, N, device=DEV, generator=g)
+    ref = X.double().t() @ G.double()
+    tol = TOL[precision] * (2 if K > 100_000 else 1)
+    assert rel(gemm.gemm_raw(X, G, trans_a=True, precision=precision), ref) < tol
+    # padded leading dimensions (views), bias + ReLU in the reduction
+    Xp = torch.randn(K, M + 8, device=DEV, generator=g)
+    Gp = torch.randn(K, N + 4, device=DEV, generator=g)
+    b = torch.randn(N, device=DEV, generator=g)
+    got = gemm.gemm_raw(Xp[:, 4:4 + M], Gp[:, :N], trans_a=True, bias=b, relu=True, precision=precision)
+    refp = torch.relu(Xp[:, 4:4 + M].double().t() @ Gp[:, :N].double() + b.double())
+    assert rel(got, refp) < tol
