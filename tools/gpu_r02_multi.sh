@@ -8,12 +8,14 @@ if [ "$3" = "tests" ]; then
   echo "pytest exit $?" >> $o/${tag}_pytest_n$N.log; tail -6 $o/${tag}_pytest_n$N.log
 fi
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517"
-for mode in "pull f32" "allgather f32" "pull bf16"; do
+IFS=";" read -ra MODES <<< "${MODES:-pull f32;allgather f32;pull bf16}"
+for mode in "${MODES[@]}"; do
   set -- $mode
   f=$o/${tag}_spmm_n${N}_$1_$2.json
   timeout 900 $TR bench.py --gpus $N --steps 20 --warmup 5 --exchange $1 --wire $2 > $f 2> ${f%.json}.err
   echo "spmm n=$N $1 $2 rc=$? $(grep -o '"ms_median": [0-9.]*\|"parity_check": {[^}]*}\|"ms_per_epoch": [0-9.]*' $f | cut -c1-160 | paste - - -)"
 done
+[ -n "$NO_REF" ] && exit 0
 f=$o/${tag}_reference_n$N.json
 timeout 600 $TR bench.py --impl reference --gpus $N --steps 3 --warmup 1 > $f 2> ${f%.json}.err
 echo "reference arm n=$N rc=$? $(grep -o '"cores": [0-9]*\|"value": [0-9.]*' $f | head -2 | paste - -)"
