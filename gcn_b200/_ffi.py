@@ -57,6 +57,8 @@ SIGNATURES = {
     "gcnb_xw_ex": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_int64, c_int, c_void_p, c_int64,
                            c_int64, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p, c_int64, ctypes.c_float,
                            ctypes.c_uint32, c_int, c_void_p]),
+    "gcnb_xw_tn_colsum": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int, c_int,
+                                  c_int, c_void_p]),
     "gcnb_dropout_keeps": (c_int, [c_int64, c_int, c_int, ctypes.c_float, ctypes.c_uint32]),
     "gcnb_logsoftmax_nll_fwd": (c_int, [c_void_p, c_int64, c_int64, c_int, c_void_p, c_void_p, c_int64, c_int64,
                                         c_void_p, c_int64, c_void_p, c_void_p]),

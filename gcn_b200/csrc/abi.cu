@@ -1,5 +1,6 @@
 // ABI bookkeeping: version, thread-local last error, device queries.
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include <mutex>
 
@@ -49,6 +50,19 @@ int sm_count(int device) {
       return 0;
     }
     cache[device] = v;
+    // Scratch of the kernels (prepared W images, partial sums) comes from the device's default stream-ordered pool.
+    // Its release threshold is 0 by default: every synchronisation hands the memory back to the driver and the
+    // next call pays for mapping it again (~1 ms for the 258 MB of partials the tall-K product once used).
+    // Keep up to GCNB_POOL_KEEP_MB (default 1024; 0 = leave the pool alone) cached instead.
+    const char* keep_env = getenv("GCNB_POOL_KEEP_MB");
+    uint64_t keep = (uint64_t)(keep_env ? atoll(keep_env) : 1024) << 20;
+    cudaMemPool_t pool;
+    if (keep > 0 && cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+      uint64_t cur = 0;
+      if (cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &cur) == cudaSuccess && cur < keep)
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
+    cudaGetLastError();
   }
   return cache[device];
 }

@@ -6,19 +6,21 @@
 // The first kernel's tall-K variant (xw_tcgen05.cu, BRAW) transposes them into K-major tiles in software
 // (4-byte transposing shared-memory stores, one 4-warp CTA) and was instruction-bound: 3.5 + 1.7 ms of the
 // 16.6 ms products-shaped epoch for 6.5 GB of operands (profiles/r02_f_launches_epoch_products.csv).
-// Blackwell's tensor core takes MN-major operands for tf32 (layout SWIZZLE_128B_BASE32B), and an MN-major operand
-// tile in that layout is exactly what a TMA box of the row-major matrix written with SWIZZLE_128B_ATOM_32B looks
-// like in shared memory (rows = k, 128-byte rows of 32 consecutive m):  no transposition at all.
-//   warp 0      producer: per stage of 16 vertices one TMA box per 32-column block of A and of B
-//   warps 4-7   converters: lo = tf32(x - trunc13(x)) for BOTH operands (both come from HBM), high part
-//               written back truncated
+// Blackwell's tensor core takes MN-major operands for tf32 (layout SWIZZLE_128B_BASE32B: rows = k, 128-byte rows
+// of 32 consecutive m), so no transposition is needed, only a re-layout of whole 16-byte chunks.
+// The first version of this kernel let TMA tensor-map boxes (16 vertices x 32 columns, SWIZZLE_128B_ATOM_32B)
+// write that layout directly; boxes made of 128-byte rows move at ~12+ cycles per row per SM (~2.5 TB/s over the
+// chip, DESIGN.md "Round 2"), so the products ran at a third of the HBM rate.  This version loads whole rows:
+//   warp 0      producer: per stage of 16 vertices ONE 1-D bulk copy per operand (16 x M x 4 contiguous bytes when
+//               the matrix is dense in memory, else one per row) into a ring of raw stages
+//   warps 4-11  converters: raw rows -> hi = trunc13(x) and lo = tf32(x - hi) tiles of BOTH operands, written
+//               as 16-byte chunks at the swizzled position of the MN-major layout (ring of 2 converted stages)
 //   warp 1      MMA issuer: per stage 2 k-steps x (hi·hi + hi·lo + lo·hi), M = 128 x N, accumulator in TMEM;
 //               the TMEM accumulator does not round to nearest, so a chain is bounded at
 //               `chain` stages (64 = 1024 vertices) and the partial is handed to the epilogue; two buffers
-//   warps 8-15  epilogue: tcgen05.ld -> partial matrix in global memory (fp32, round-to-nearest sums later)
+//   warps 12-19 epilogue: tcgen05.ld -> partial matrix in global memory (fp32, round-to-nearest sums later)
 //   The partials of all CTAs are added in a fixed order by xt_reduce_kernel (also transposes the result
 //   when the caller's M exceeded 128 and the product was computed as (G^T · X)^T).
-#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdlib.h>
@@ -32,24 +34,30 @@ namespace gcnb {
 namespace xt {
 
 constexpr int KV = 16;                 // vertices (k) per stage
-constexpr int BLK = KV * 128;          // bytes of one 32-column block of a stage (KV rows x 128 B)
+constexpr int BLK = KV * 128;          // bytes of one 32-column block of a converted stage (KV rows x 128 B)
 constexpr int A_BLOCKS = 4, B_BLOCKS = 8;
-constexpr int STAGE = (A_BLOCKS + B_BLOCKS) * BLK;   // 24 KB
-constexpr int RAW = 5, LO = 3;         // ring depths
-constexpr int NE = 8;
-constexpr int THREADS = (8 + NE) * 32;
-constexpr int SMEM = (RAW + LO) * STAGE + 1024 + 1024;
+constexpr int PART = (A_BLOCKS + B_BLOCKS) * BLK;    // hi (or lo) tiles of one stage: 24 KB
+constexpr int CONV_STAGE = 2 * PART;                 // hi | lo
+constexpr int CS = 2;                  // converted stages in flight
+constexpr int RAW_MAX = 8;             // raw stages in flight (barrier slots)
+constexpr int NC = 8, NE = 8;          // converter / epilogue warps
+constexpr int THREADS = (4 + NC + NE) * 32;
+constexpr int SMEM_MAX = 232448;
 
 struct Params {
-  float* part;               // [n_part][M][N] partial matrices
+  const float* A; int64_t lda;   // [K x M] row-major, the operand whose columns become the rows of D
+  const float* B; int64_t ldb;   // [K x N] row-major
+  float* part;               // [grid][rows][N] one partial matrix per CTA (rows = M, +1 with the ones column)
   int64_t K;                 // vertices
-  int M, N;                  // used rows / columns (M <= 128, N <= 256)
+  int M, N;                  // used rows / columns (M <= 128, N <= 256, both multiples of 4)
+  int M1;                    // rows of a partial matrix: M, or ones_col + 1
   int mb, nb;                // 32-column blocks of A / B in use
   int64_t v_per_cta;         // vertices per CTA (multiple of KV)
-  int chain;                 // stages per partial
-  int parts_per_cta;
-  uint32_t desc_layout;      // shared-memory descriptor layout type (2 = SWIZZLE_128B, 1 = SWIZZLE_128B_BASE32B)
-  uint32_t desc_sbo;         // stride byte offset (bytes between k-atoms)
+  int chain;                 // stages per accumulation chain in TMEM
+  int ones_col;              // -1, or the column of A (>= M, < 128) the converters fill with 1.0: row `ones_col`
+                             // of the product is then the column sums of B (the bias gradient next to dW)
+  int raws;                  // raw stages in flight
+  int raw_stage;             // bytes of one raw stage: KV x (M + N) floats, rounded up to 128
 };
 
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -63,19 +71,37 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         : "=r"(done) : "r"(bar), "r"(parity) : "memory");
   }
 }
+__device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  while (true) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    if (done) break;
+    __nanosleep(256);
+  }
+}
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
-// MN-major SWIZZLE_128B operand: 8 k-rows x 128 B per atom; `lbo` = bytes between consecutive 32-element
-// blocks in M/N, stride byte offset = next 8 k-rows (unused by a K = 8 instruction)
-__device__ __forceinline__ uint64_t make_desc_mn(uint32_t saddr, uint32_t lbo, uint32_t sbo, uint32_t layout) {
+// MN-major tf32 operand, layout SWIZZLE_128B_BASE32B (type 1): rows = k, 128 bytes (32 consecutive m) per row, the
+// 32-byte units of a row XOR-ed with (row & 3); 4-row k-atoms 512 bytes apart; `lbo` = bytes between consecutive
+// 32-element blocks in M/N.  Pinned on hardware (profiles/r02_j_xt_variants.jsonl): with the plain SWIZZLE_128B
+// layout the tensor core returns zeros for MN-major tf32.
+__device__ __forceinline__ uint64_t make_desc_mn(uint32_t saddr, uint32_t lbo) {
   uint64_t d = 0;
   d |= (uint64_t)((saddr >> 4) & 0x3fff);
   d |= (uint64_t)((lbo >> 4) & 0x3fff) << 16;
-  d |= (uint64_t)((sbo >> 4) & 0x3fff) << 32;
+  d |= (uint64_t)(512 >> 4) << 32;
   d |= (uint64_t)1 << 46;
-  d |= (uint64_t)(layout & 7) << 61;
+  d |= (uint64_t)1 << 61;
   return d;
+}
+// byte offset of the 16-byte chunk (k-row v, chunk c16 of the 128-byte row) inside a block
+__device__ __forceinline__ uint32_t mn_off(int v, int c16) {
+  return (uint32_t)(v * 128 + ((((c16 >> 1) ^ (v & 3)) << 5) | ((c16 & 1) << 4)));
 }
 // D fp32, A/B TF32, both MN-major (bits 15, 16), M = 128, N = n
 __device__ __forceinline__ uint32_t make_idesc(int n) {
@@ -96,41 +122,36 @@ __device__ __forceinline__ uint32_t to_tf32(float x) {
   return r;
 }
 
-}  // namespace xt
-}  // namespace gcnb
-
-namespace gcnb {
-namespace xt {
-
 template <int MODE>   // 0: 3xTF32, 1: single-pass TF32
 __global__ void __launch_bounds__(THREADS, 1)
-xt_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, const Params p) {
+xt_kernel(const Params p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_addr(smem_raw) & 1023u)) & 1023u);
-  uint8_t* raw = smem;                         // RAW stages: [A blocks 0..3 | B blocks 0..7], block = KV rows x 128 B
-  uint8_t* lo = raw + RAW * STAGE;             // LO stages, same layout
-  uint64_t* bars = reinterpret_cast<uint64_t*>(lo + LO * STAGE);
-  // bars: FULL[RAW] EMPTY[RAW] CONV[LO] LOEMPTY[LO] TFULL[2] TEMPTY[2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * RAW + 2 * LO + 4);
+  uint8_t* conv = smem;                        // CS stages: { hi: A blocks 0..3 | B blocks 0..7 } { lo: same }
+  uint8_t* raw = conv + CS * CONV_STAGE;       // raws stages: A rows [KV][M] then B rows [KV][N], row-major
+  uint64_t* bars = reinterpret_cast<uint64_t*>(raw + p.raws * p.raw_stage);
+  // bars: FULL[RAW_MAX] EMPTY[RAW_MAX] CONV[CS] CEMPTY[CS] TFULL[2] TEMPTY[2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * RAW_MAX + 2 * CS + 4);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t bar0 = smem_addr(bars);
   auto FULL = [&](int s) { return bar0 + 8u * (uint32_t)s; };
-  auto EMPTY = [&](int s) { return bar0 + 8u * (uint32_t)(RAW + s); };
-  auto CONV = [&](int s) { return bar0 + 8u * (uint32_t)(2 * RAW + s); };
-  auto LOEMPTY = [&](int s) { return bar0 + 8u * (uint32_t)(2 * RAW + LO + s); };
-  auto TFULL = [&](int b) { return bar0 + 8u * (uint32_t)(2 * RAW + 2 * LO + b); };
-  auto TEMPTY = [&](int b) { return bar0 + 8u * (uint32_t)(2 * RAW + 2 * LO + 2 + b); };
+  auto EMPTY = [&](int s) { return bar0 + 8u * (uint32_t)(RAW_MAX + s); };
+  auto CONV = [&](int s) { return bar0 + 8u * (uint32_t)(2 * RAW_MAX + s); };
+  auto CEMPTY = [&](int s) { return bar0 + 8u * (uint32_t)(2 * RAW_MAX + CS + s); };
+  auto TFULL = [&](int b) { return bar0 + 8u * (uint32_t)(2 * RAW_MAX + 2 * CS + b); };
+  auto TEMPTY = [&](int b) { return bar0 + 8u * (uint32_t)(2 * RAW_MAX + 2 * CS + 2 + b); };
   const int n_umma = p.nb * 32;                // UMMA N (multiple of 32, <= 256)
   constexpr int TMEM_COLS = 512;               // two accumulator buffers of up to 256 columns
+  const int RAWS = p.raws;
 
   if (tid == 0) {
-    for (int s = 0; s < RAW; ++s) {
+    for (int s = 0; s < RAW_MAX; ++s) {
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(FULL(s)));
-      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(EMPTY(s)));
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(EMPTY(s)), "r"(NC * 32));
     }
-    for (int s = 0; s < LO; ++s) {
-      asm volatile("mbarrier.init.shared::cta.b64 [%0], 128;" ::"r"(CONV(s)));
-      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(LOEMPTY(s)));
+    for (int s = 0; s < CS; ++s) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(CONV(s)), "r"(NC * 32));
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(CEMPTY(s)));
     }
     for (int b = 0; b < 2; ++b) {
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(TFULL(b)));
@@ -138,9 +159,9 @@ xt_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  // blocks of A beyond the used ones are never loaded: zero them once, in the raw and the lo stages (the MMA
-  // always runs at M = 128); the converters keep zeros zero
-  for (int i = tid; i < (RAW + LO) * STAGE / 16; i += THREADS) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+  // the converted tiles are zeroed once: the converters never write the columns past M / N of the last block
+  // nor the blocks past mb / nb (the MMA always runs at M = 128), so those stay zero for the whole kernel
+  for (int i = tid; i < CS * CONV_STAGE / 16; i += THREADS) reinterpret_cast<uint4*>(conv)[i] = make_uint4(0, 0, 0, 0);
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   if (warp == 1) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
@@ -158,24 +179,35 @@ xt_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
   const int ngroups = (nst + p.chain - 1) / p.chain;                 // partials it produces
 
   if (warp == 0) {
-    // ---------------- producer ----------------
+    // ---------------- producer: 1-D bulk copies of whole rows (one per operand and stage when the rows are
+    // contiguous, else one per row) — the TMA unit moves large contiguous ranges at full rate, while tensor-map
+    // boxes of 128-byte rows (the first version of this kernel) are limited to ~12 cycles per row per SM ----------------
     if (lane == 0) {
-      const uint32_t bytes = (uint32_t)((p.mb + p.nb) * BLK);
+      const bool a_contig = p.lda == p.M, b_contig = p.ldb == p.N;
       for (int it = 0; it < nst; ++it) {
-        const int s = it % RAW;
-        mbar_wait(EMPTY(s), ((it / RAW) & 1) ^ 1);
+        const int s = it % RAWS;
+        mbar_wait(EMPTY(s), ((it / RAWS) & 1) ^ 1);
+        const int64_t v = v0 + (int64_t)it * KV;
+        const int rows = (int)(v1 - v < KV ? v1 - v : KV);
         const uint32_t full = FULL(s);
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(full), "r"(bytes) : "memory");
-        const int v = (int)(v0 + (int64_t)it * KV);
-        const uint32_t dst = smem_addr(raw + s * STAGE);
-        for (int b = 0; b < p.mb; ++b)
-          asm volatile(
-              "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-              ::"r"(dst + b * BLK), "l"(&tmap_a), "r"(b * 32), "r"(v), "r"(full) : "memory");
-        for (int b = 0; b < p.nb; ++b)
-          asm volatile(
-              "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-              ::"r"(dst + (A_BLOCKS + b) * BLK), "l"(&tmap_b), "r"(b * 32), "r"(v), "r"(full) : "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(full), "r"((uint32_t)(rows * (p.M + p.N) * 4)) : "memory");
+        const uint32_t dst_a = smem_addr(raw + s * p.raw_stage), dst_b = dst_a + (uint32_t)(KV * p.M * 4);
+        if (a_contig) {
+          asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                       ::"r"(dst_a), "l"(p.A + v * p.lda), "r"((uint32_t)(rows * p.M * 4)), "r"(full) : "memory");
+        } else {
+          for (int r = 0; r < rows; ++r)
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(dst_a + (uint32_t)(r * p.M * 4)), "l"(p.A + (v + r) * p.lda), "r"((uint32_t)(p.M * 4)), "r"(full) : "memory");
+        }
+        if (b_contig) {
+          asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                       ::"r"(dst_b), "l"(p.B + v * p.ldb), "r"((uint32_t)(rows * p.N * 4)), "r"(full) : "memory");
+        } else {
+          for (int r = 0; r < rows; ++r)
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(dst_b + (uint32_t)(r * p.N * 4)), "l"(p.B + (v + r) * p.ldb), "r"((uint32_t)(p.N * 4)), "r"(full) : "memory");
+        }
       }
     }
   } else if (warp == 1) {
@@ -190,65 +222,81 @@ xt_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         }
         const uint32_t tmem_d = tmem_base + buf * 256;
-        const int s = it % RAW, sl = it % LO;
-        mbar_wait(FULL(s), (it / RAW) & 1);
-        if constexpr (MODE == 0) mbar_wait(CONV(sl), (it / LO) & 1);
+        const int cs = it % CS;
+        mbar_wait(CONV(cs), (it / CS) & 1);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint32_t a_hi = smem_addr(raw + s * STAGE), b_hi = a_hi + A_BLOCKS * BLK;
-        const uint32_t a_lo = smem_addr(lo + sl * STAGE), b_lo = a_lo + A_BLOCKS * BLK;
+        const uint32_t a_hi = smem_addr(conv + cs * CONV_STAGE), b_hi = a_hi + A_BLOCKS * BLK;
+        const uint32_t a_lo = a_hi + PART, b_lo = a_lo + A_BLOCKS * BLK;
 #pragma unroll
-        for (int ks = 0; ks < KV / 8; ++ks) {        // 8 vertices per MMA: one 8-row swizzle atom of every block
+        for (int ks = 0; ks < KV / 8; ++ks) {        // 8 vertices per MMA: two 4-row k-atoms of every block
           const uint32_t o = ks * 1024;
           const uint32_t acc = (pos > 0 || ks > 0) ? 1u : 0u;
-          const uint32_t sb = p.desc_sbo, ly = p.desc_layout;
-          mma_tf32(tmem_d, make_desc_mn(a_hi + o, BLK, sb, ly), make_desc_mn(b_hi + o, BLK, sb, ly), idesc, acc);
+          mma_tf32(tmem_d, make_desc_mn(a_hi + o, BLK), make_desc_mn(b_hi + o, BLK), idesc, acc);
           if constexpr (MODE == 0) {
-            mma_tf32(tmem_d, make_desc_mn(a_hi + o, BLK, sb, ly), make_desc_mn(b_lo + o, BLK, sb, ly), idesc, 1u);
-            mma_tf32(tmem_d, make_desc_mn(a_lo + o, BLK, sb, ly), make_desc_mn(b_hi + o, BLK, sb, ly), idesc, 1u);
+            mma_tf32(tmem_d, make_desc_mn(a_hi + o, BLK), make_desc_mn(b_lo + o, BLK), idesc, 1u);
+            mma_tf32(tmem_d, make_desc_mn(a_lo + o, BLK), make_desc_mn(b_hi + o, BLK), idesc, 1u);
           }
         }
-        commit(EMPTY(s));
-        if constexpr (MODE == 0) commit(LOEMPTY(sl));
+        commit(CEMPTY(cs));
         if (pos == p.chain - 1 || it == nst - 1) commit(TFULL(buf));
       }
     }
-  } else if (warp >= 4 && warp < 8) {
-    // ---------------- converters: both operands ----------------
-    if constexpr (MODE == 0) {
-      const int ct = tid - 128;
-      for (int it = 0; it < nst; ++it) {
-        const int s = it % RAW, sl = it % LO;
-        mbar_wait(FULL(s), (it / RAW) & 1);
-        mbar_wait(LOEMPTY(sl), ((it / LO) & 1) ^ 1);
-        uint8_t* r = raw + s * STAGE;
-        uint8_t* l = lo + sl * STAGE;
-#pragma unroll 4
-        for (int j = 0; j < STAGE / 16 / 128; ++j) {
-          const int off = (ct + j * 128) * 16;
-          const uint4 v = *reinterpret_cast<const uint4*>(r + off);
-          uint4 o;
-          o.x = to_tf32(__uint_as_float(v.x) - __uint_as_float(v.x & 0xffffe000u));
-          o.y = to_tf32(__uint_as_float(v.y) - __uint_as_float(v.y & 0xffffe000u));
-          o.z = to_tf32(__uint_as_float(v.z) - __uint_as_float(v.z & 0xffffe000u));
-          o.w = to_tf32(__uint_as_float(v.w) - __uint_as_float(v.w & 0xffffe000u));
-          *reinterpret_cast<uint4*>(l + off) = o;
-          *reinterpret_cast<uint4*>(r + off) =
-              make_uint4(v.x & 0xffffe000u, v.y & 0xffffe000u, v.z & 0xffffe000u, v.w & 0xffffe000u);
+  } else if (warp >= 4 && warp < 4 + NC) {
+    // ---------------- converters: raw rows -> MN-major hi / lo tiles (both operands) ----------------
+    const int ct = tid - 128;                        // 0 .. NC*32-1
+    const int mpc = p.M >> 2, npc = p.N >> 2;        // 16-byte chunks per row
+    const uint32_t inv_m = (65536u + (uint32_t)mpc - 1) / (uint32_t)mpc, inv_n = (65536u + (uint32_t)npc - 1) / (uint32_t)npc;
+    for (int it = 0; it < nst; ++it) {
+      const int s = it % RAWS, cs = it % CS;
+      mbar_wait(FULL(s), (it / RAWS) & 1);
+      mbar_wait(CEMPTY(cs), ((it / CS) & 1) ^ 1);
+      const int64_t v = v0 + (int64_t)it * KV;
+      const int rows = (int)(v1 - v < KV ? v1 - v : KV);
+      const uint8_t* ra = raw + s * p.raw_stage;
+      const uint8_t* rb = ra + KV * p.M * 4;
+      uint8_t* hi = conv + cs * CONV_STAGE;
+      uint8_t* lo = hi + PART;
+      auto convert = [&](const uint8_t* src, int cols4, uint32_t inv, uint8_t* dhi, uint8_t* dlo) {
+        for (int i = ct; i < KV * cols4; i += NC * 32) {
+          const int vr = (int)(((uint32_t)i * inv) >> 16);          // i / cols4 (exact for i < 1024, cols4 <= 64)
+          const int c = i - vr * cols4;
+          uint4 x = make_uint4(0, 0, 0, 0);
+          if (vr < rows) x = *reinterpret_cast<const uint4*>(src + (size_t)i * 16);   // rows past the end of K are zero
+          const uint4 h = make_uint4(x.x & 0xffffe000u, x.y & 0xffffe000u, x.z & 0xffffe000u, x.w & 0xffffe000u);
+          const uint32_t off = (uint32_t)((c >> 3) * BLK) + mn_off(vr, c & 7);
+          *reinterpret_cast<uint4*>(dhi + off) = h;
+          if constexpr (MODE == 0) {
+            uint4 l;
+            l.x = to_tf32(__uint_as_float(x.x) - __uint_as_float(h.x));
+            l.y = to_tf32(__uint_as_float(x.y) - __uint_as_float(h.y));
+            l.z = to_tf32(__uint_as_float(x.z) - __uint_as_float(h.z));
+            l.w = to_tf32(__uint_as_float(x.w) - __uint_as_float(h.w));
+            *reinterpret_cast<uint4*>(dlo + off) = l;
+          }
         }
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        mbar_arrive(CONV(sl));
+      };
+      convert(ra, mpc, inv_m, hi, lo);
+      convert(rb, npc, inv_n, hi + A_BLOCKS * BLK, lo + A_BLOCKS * BLK);
+      if (p.ones_col >= 0 && ct < KV) {            // A[v, ones_col] = 1 for the vertices that exist (its low part stays 0)
+        const int c = p.ones_col >> 2;
+        *reinterpret_cast<float*>(hi + (c >> 3) * BLK + mn_off(ct, c & 7) + (p.ones_col & 3) * 4) = ct < rows ? 1.f : 0.f;
       }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic stores -> tensor core's proxy
+      mbar_arrive(CONV(cs));
+      mbar_arrive(EMPTY(s));                          // this thread's reads of the raw stage are done
     }
-  } else if (warp >= 8) {
+  } else if (warp >= 4 + NC) {
     // ---------------- epilogue: accumulator -> partial matrix ----------------
-    const int q = warp & 3, eg = (warp - 8) >> 2;
+    const int q = warp & 3, eg = (warp - 4 - NC) >> 2;
     const int row = q * 32 + lane;                   // row of D = column of A
     for (int grp = 0; grp < ngroups; ++grp) {
       const uint32_t buf = grp & 1;
-      mbar_wait(TFULL(buf), (grp >> 1) & 1);
+      mbar_wait_sleep(TFULL(buf), (grp >> 1) & 1);   // a chain takes tens of microseconds: do not spin on the issue slots
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const uint32_t taddr0 = tmem_base + buf * 256 + ((uint32_t)(q * 32) << 16);
-      float* dst = p.part + ((int64_t)blockIdx.x * p.parts_per_cta + grp) * (int64_t)p.M * p.N + (int64_t)row * p.N;
+      // one partial matrix per CTA, accumulated chain by chain by the thread that owns the row (L2-resident,
+      // 100 KB per CTA): round-to-nearest fp32 sums in a fixed order, and the final reduction reads 148 partials
+      float* dst = p.part + (int64_t)blockIdx.x * p.M1 * p.N + (int64_t)row * p.N;
 #pragma unroll 1
       for (int c0 = eg * 32; c0 < n_umma; c0 += (NE / 4) * 32) {
         uint32_t r[32];
@@ -263,10 +311,17 @@ xt_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
               "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
             : "r"(taddr0 + (uint32_t)(c0 + 16)) : "memory");
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-        if (row < p.M) {
+        if (row < p.M1) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (c0 + j < p.N) dst[c0 + j] = __uint_as_float(r[j]);
+          for (int j = 0; j < 32; j += 4) {
+            if (c0 + j < p.N) {                      // N is a multiple of 4
+              float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (grp > 0) o = *reinterpret_cast<const float4*>(dst + c0 + j);
+              o.x += __uint_as_float(r[j]); o.y += __uint_as_float(r[j + 1]);
+              o.z += __uint_as_float(r[j + 2]); o.w += __uint_as_float(r[j + 3]);
+              *reinterpret_cast<float4*>(dst + c0 + j) = o;
+            }
+          }
         }
       }
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -279,25 +334,24 @@ xt_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
 }
 
-// D (+bias)(ReLU) = sum of the partial matrices in a fixed order (CTA by CTA, chain by chain); `transposed`:
-// the partials are [N x M] = D^T
+// D (+bias)(ReLU) = sum of the CTAs' partial matrices in a fixed order; `transposed`: the partials are [N x M] = D^T.
+// Row M of the partials (ones column, direct route only) goes to colsum[0..N).
 __global__ void __launch_bounds__(256)
-xt_reduce_kernel(const float* __restrict__ part, int n_cta, int parts_per_cta, int64_t K, int64_t v_per_cta, int chain,
-                 int Mp, int Np, int transposed, float* __restrict__ D, int64_t ldd, int M, int N,
-                 const float* __restrict__ bias, int epi) {
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;     // element of the partial matrix (Mp x Np)
-  if (idx >= Mp * Np) return;
+xt_reduce_kernel(const float* __restrict__ part, int n_cta, int64_t K, int64_t v_per_cta, int M1, int Mp, int Np,
+                 int transposed, float* __restrict__ D, int64_t ldd, int M, int N, const float* __restrict__ bias,
+                 int epi, int ones_row, float* __restrict__ colsum) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;     // element of the partial matrix (M1 x Np)
+  if (idx >= M1 * Np) return;
   float s = 0.f;
   for (int c = 0; c < n_cta; ++c) {
-    const int64_t v0 = (int64_t)c * v_per_cta;
-    if (v0 >= K) break;
-    const int64_t v1 = v0 + v_per_cta < K ? v0 + v_per_cta : K;
-    const int nst = (int)((v1 - v0 + KV - 1) / KV);
-    const int np = (nst + chain - 1) / chain;
-    const float* base = part + ((int64_t)c * parts_per_cta) * Mp * Np + idx;
-    for (int g = 0; g < np; ++g) s += base[(int64_t)g * Mp * Np];
+    if ((int64_t)c * v_per_cta >= K) break;                   // trailing CTAs without vertices wrote nothing
+    s += part[(int64_t)c * M1 * Np + idx];
   }
   const int pr = idx / Np, pc = idx % Np;
+  if (pr >= Mp) {
+    if (pr == ones_row && colsum) colsum[pc] = s;
+    return;
+  }
   const int r = transposed ? pc : pr, c = transposed ? pr : pc;
   if (r >= M || c >= N) return;
   if (epi & GCNB_EPI_BIAS) s += __ldg(bias + c);
@@ -311,91 +365,57 @@ xt_reduce_kernel(const float* __restrict__ part, int n_cta, int parts_per_cta, i
 // ---- host side ---------------------------------------------------------------------------------------
 namespace gcnb {
 
-typedef CUresult (*EncodeTiledFn2)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn2 encode_tiled2() {
-  static std::atomic<EncodeTiledFn2> fn{nullptr};
-  EncodeTiledFn2 f = fn.load(std::memory_order_acquire);
-  if (!f) {
-    void* ptr = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
-        q == cudaDriverEntryPointSuccess)
-      f = (EncodeTiledFn2)ptr;
-    fn.store(f, std::memory_order_release);
-  }
-  return f;
-}
-
-static bool xt_map(EncodeTiledFn2 enc, CUtensorMap* m, const float* base, int64_t ld, int cols, int64_t rows,
-                   CUtensorMapSwizzle swz) {
-  const cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-  const cuuint64_t gstride[1] = {(cuuint64_t)ld * 4};
-  const cuuint32_t box[2] = {32, (cuuint32_t)xt::KV};
-  const cuuint32_t estr[2] = {1, 1};
-  return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-             swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
-}
-
 // D[M x N] = X^T · W with X stored [K x M] (leading dimension ldx) and W stored [K x N] (ldw).
 // Returns GCNB_OK when the product ran here, 1 when the shape is not this kernel's (caller falls back).
+// colsum (optional): receives 1^T·W, the column sums of W, from the same pass (ones column in the X operand);
+// returns 1 when that cannot be done here (no spare row in the 128-row tile).
 int xw_tallk_stream_run(const float* X, int64_t ldx, const float* W, int64_t ldw, float* D, int64_t ldd, int64_t M,
-                        int N, int64_t K, const float* bias, int epi, int precision, int n_sm, cudaStream_t stream) {
+                        int N, int64_t K, const float* bias, int epi, int precision, int n_sm, float* colsum,
+                        cudaStream_t stream) {
   static const int enabled = getenv("GCNB_XW_TALLK_STREAM") ? atoi(getenv("GCNB_XW_TALLK_STREAM")) : 1;
   if (!enabled || precision > 1 || K < 4096 || K >= ((int64_t)1 << 31) || M < 1 || N < 1) return 1;
-  if (((uintptr_t)X & 15) || ((uintptr_t)W & 15) || (ldx % 4) != 0 || (ldw % 4) != 0) return 1;
+  // whole rows travel as 16-byte-granular bulk copies
+  if (((uintptr_t)X & 15) || ((uintptr_t)W & 15) || (ldx % 4) != 0 || (ldw % 4) != 0 || (M % 4) != 0 || (N % 4) != 0) return 1;
   const bool direct = M <= 128 && N <= 256;
   const bool swapped = !direct && N <= 128 && M <= 256;
   if (!direct && !swapped) return 1;
-  EncodeTiledFn2 enc = encode_tiled2();
-  if (!enc) return 1;
-  // operand A (<= 128 columns -> rows of the accumulator), operand B (<= 256 columns)
-  const float* A = direct ? X : W;
-  const float* B = direct ? W : X;
-  const int64_t lda = direct ? ldx : ldw, ldb = direct ? ldw : ldx;
-  const int Mp = direct ? (int)M : N, Np = direct ? N : (int)M;
-  // operand layout, pinned down on hardware (profiles/r02_j_xt_variants.jsonl): MN-major tf32 operands need the
-  // 32-byte-atom flavour of the 128-byte swizzle on both sides — TMA CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B and the
-  // descriptor layout SWIZZLE_128B_BASE32B (type 1) with 4-row k-atoms 512 bytes apart: error 7.5e-7 .. 3.4e-6 of
-  // fp64.  The plain SWIZZLE_128B pair (variant 0) and mixed pairs (3) make the tensor core return ZEROS, the right
-  // pair with a 1024-byte atom stride (2) garbage.  GCNB_XT_VARIANT keeps the other three reachable.
-  const char* var_env = getenv("GCNB_XT_VARIANT");
-  const int variant = var_env ? atoi(var_env) : 1;
-  const CUtensorMapSwizzle swz = (variant == 0) ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B;
-  CUtensorMap ta, tb;
-  if (!xt_map(enc, &ta, A, lda, Mp, K, swz) || !xt_map(enc, &tb, B, ldb, Np, K, swz)) return 1;
+  if (colsum && !(direct && M < 128)) return 1;
   xt::Params p;
-  p.desc_layout = (variant == 1 || variant == 2) ? 1u : 2u;
-  p.desc_sbo = (variant == 1) ? 512u : 1024u;
+  p.A = direct ? X : W; p.lda = direct ? ldx : ldw;
+  p.B = direct ? W : X; p.ldb = direct ? ldw : ldx;
+  const int Mp = direct ? (int)M : N, Np = direct ? N : (int)M;
   p.K = K; p.M = Mp; p.N = Np; p.mb = (Mp + 31) / 32; p.nb = (Np + 31) / 32;
+  p.ones_col = colsum ? Mp : -1;
+  p.M1 = colsum ? Mp + 1 : Mp;
+  p.raw_stage = ((xt::KV * (Mp + Np) * 4) + 127) & ~127;
+  p.raws = std::min(xt::RAW_MAX, (xt::SMEM_MAX - xt::CS * xt::CONV_STAGE - 2048) / p.raw_stage);
+  if (p.raws < 2) return 1;
+  const int smem = xt::CS * xt::CONV_STAGE + p.raws * p.raw_stage + 2048;
   const int64_t stages_total = (K + xt::KV - 1) / xt::KV;
   const int grid = (int)std::min<int64_t>(n_sm, stages_total);
   const int64_t st_per_cta = (stages_total + grid - 1) / grid;
   p.v_per_cta = st_per_cta * xt::KV;
   const char* chain_env = getenv("GCNB_XW_MAX_CHAIN");
-  p.chain = std::max(1, chain_env ? atoi(chain_env) : 64);
-  p.parts_per_cta = (int)((st_per_cta + p.chain - 1) / p.chain);
+  p.chain = std::max(1, chain_env ? atoi(chain_env) : 32);
   float* part = nullptr;
-  GCNB_CHECK_CUDA(cudaMallocAsync(&part, (size_t)grid * p.parts_per_cta * Mp * Np * sizeof(float), stream));
+  GCNB_CHECK_CUDA(cudaMallocAsync(&part, (size_t)grid * p.M1 * Np * sizeof(float), stream));
   p.part = part;
   static std::atomic<uint64_t> configured{0};
   int dev = 0;
   GCNB_CHECK_CUDA(cudaGetDevice(&dev));
   const uint64_t bit = 1ull << (dev & 63);
   if (dev >= 64 || !(configured.load(std::memory_order_relaxed) & bit)) {
-    GCNB_CHECK_CUDA(cudaFuncSetAttribute(xt::xt_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, xt::SMEM));
-    GCNB_CHECK_CUDA(cudaFuncSetAttribute(xt::xt_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, xt::SMEM));
+    GCNB_CHECK_CUDA(cudaFuncSetAttribute(xt::xt_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, xt::SMEM_MAX));
+    GCNB_CHECK_CUDA(cudaFuncSetAttribute(xt::xt_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, xt::SMEM_MAX));
     configured.fetch_or(bit, std::memory_order_relaxed);
   }
-  if (precision == 0) xt::xt_kernel<0><<<grid, xt::THREADS, xt::SMEM, stream>>>(ta, tb, p);
-  else xt::xt_kernel<1><<<grid, xt::THREADS, xt::SMEM, stream>>>(ta, tb, p);
+  if (precision == 0) xt::xt_kernel<0><<<grid, xt::THREADS, smem, stream>>>(p);
+  else xt::xt_kernel<1><<<grid, xt::THREADS, smem, stream>>>(p);
   int rc = GCNB_OK;
   if (cudaGetLastError() != cudaSuccess) rc = set_error(GCNB_ERR_CUDA, "xt_kernel launch failed");
   if (rc == GCNB_OK) {
-    xt::xt_reduce_kernel<<<(unsigned)((Mp * Np + 255) / 256), 256, 0, stream>>>(
-        part, grid, p.parts_per_cta, K, p.v_per_cta, p.chain, Mp, Np, direct ? 0 : 1, D, ldd, (int)M, N, bias, epi);
+    xt::xt_reduce_kernel<<<(unsigned)((p.M1 * Np + 255) / 256), 256, 0, stream>>>(
+        part, grid, K, p.v_per_cta, p.M1, Mp, Np, direct ? 0 : 1, D, ldd, (int)M, N, bias, epi, p.ones_col, colsum);
     if (cudaGetLastError() != cudaSuccess) rc = set_error(GCNB_ERR_CUDA, "xt_reduce_kernel launch failed");
   }
   cudaFreeAsync(part, stream);

@@ -517,8 +517,39 @@ int xw_stream_run(const float* X, int64_t ldx, const float* W, int64_t ldw, int 
                   int64_t M, int N, int K, const float* bias, int epi, const uint32_t* mask_in, uint32_t* mask_out,
                   int64_t ldm, float drop_p, uint32_t seed, int precision, int n_sm, cudaStream_t stream);   // xw_stream.cu
 int xw_tallk_stream_run(const float* X, int64_t ldx, const float* W, int64_t ldw, float* D, int64_t ldd, int64_t M,
-                        int N, int64_t K, const float* bias, int epi, int precision, int n_sm,
+                        int N, int64_t K, const float* bias, int epi, int precision, int n_sm, float* colsum,
                         cudaStream_t stream);                                                              // xw_tallk_stream.cu
+// column sums of a row-major [K x N] matrix in two fixed-order passes (the fall-back of gcnb_xw_tn_colsum when
+// the product kernel has no spare row for the ones column): slabs of kColsumRows rows -> part[slab][N] -> out[N]
+constexpr int kColsumRows = 4096;
+__global__ void __launch_bounds__(256)
+colsum_slab_kernel(const float* __restrict__ G, int64_t ldg, int64_t K, int N, float* __restrict__ part) {
+  __shared__ float sh[8][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int64_t r0 = (int64_t)blockIdx.x * kColsumRows, r1 = r0 + kColsumRows < K ? r0 + kColsumRows : K;
+  for (int c0 = 0; c0 < N; c0 += 32) {
+    float s = 0.f;
+    if (c0 + tx < N)
+      for (int64_t r = r0 + ty; r < r1; r += 8) s += G[r * ldg + c0 + tx];
+    sh[ty][tx] = s;
+    __syncthreads();
+    if (ty == 0 && c0 + tx < N) {
+      float t = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) t += sh[j][tx];
+      part[(int64_t)blockIdx.x * N + c0 + tx] = t;
+    }
+    __syncthreads();
+  }
+}
+__global__ void __launch_bounds__(256)
+colsum_final_kernel(const float* __restrict__ part, int slabs, int N, float* __restrict__ out) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= N) return;
+  float s = 0.f;
+  for (int b = 0; b < slabs; ++b) s += part[(int64_t)b * N + c];
+  out[c] = s;
+}
 // elementwise tail of gcnb_xw_ex for the products that do not run on the streaming kernel: one thread per
 // (row, 32-column word of the bit masks); same dropout hash (one word per 4 columns, one byte per element)
 __global__ void __launch_bounds__(256)
@@ -609,7 +640,7 @@ extern "C" int gcnb_xw_ex(const float* X, int64_t ldx, int trans_x, const float*
   }
 
   if (K > 0 && trans_x && !trans_w) {   // dW = X^T·G with both operands row-major over the vertices
-    const int r = xw_tallk_stream_run(X, ldx, W, ldw, D, ldd, M, N, K, bias, epilogue, precision, sm_count(dev), stream);
+    const int r = xw_tallk_stream_run(X, ldx, W, ldw, D, ldd, M, N, K, bias, epilogue, precision, sm_count(dev), nullptr, stream);
     if (r == GCNB_OK) return run_tail();
     if (r != 1) return r;
   }
@@ -697,5 +728,46 @@ extern "C" int gcnb_xw_ex(const float* X, int64_t ldx, int trans_x, const float*
   if (img) cudaFreeAsync(img, stream);
   if (partial) cudaFreeAsync(partial, stream);
   if (rc == GCNB_OK) rc = run_tail();
+  return rc;
+}
+
+extern "C" int gcnb_xw_tn_colsum(const float* X, int64_t ldx, const float* G, int64_t ldg, float* D, int64_t ldd,
+                                 float* colsum, int64_t M, int N, int K, int precision, void* stream_) {
+  GCNB_REQUIRE(M >= 0 && N >= 0 && K >= 0, "negative size (M=%lld N=%d K=%d)", (long long)M, N, K);
+  GCNB_REQUIRE(precision >= 0 && precision <= 2, "precision %d not in 0..2", precision);
+  GCNB_REQUIRE(N == 0 || colsum != nullptr, "colsum is null");
+  if (N == 0) return GCNB_OK;
+  int rc = require_gpu();
+  if (rc != GCNB_OK) return rc;
+  const int dev = pointer_device(colsum);
+  GCNB_REQUIRE(dev >= 0, "colsum is not a device pointer");
+  DeviceGuard guard(dev);
+  GCNB_CHECK_CUDA(guard.status);
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (M > 0 && K > 0) {
+    GCNB_REQUIRE(D != nullptr && ldd >= N && X != nullptr && G != nullptr && ldx >= M && ldg >= N,
+                 "null operand or leading dimension smaller than the stored row length");
+    const int r = xw_tallk_stream_run(X, ldx, G, ldg, D, ldd, M, N, K, nullptr, 0, precision, sm_count(dev), colsum, stream);
+    if (r != 1) return r;   // both results came out of the one pass (or it failed)
+  }
+  if (M > 0) {
+    rc = gcnb_xw_ex(X, ldx, 1, G, ldg, 0, D, ldd, M, N, K, nullptr, 0, nullptr, nullptr, 0, 0.f, 0, precision, stream_);
+    if (rc != GCNB_OK) return rc;
+  }
+  if (K == 0) {
+    GCNB_CHECK_CUDA(cudaMemsetAsync(colsum, 0, (size_t)N * sizeof(float), stream));
+    return GCNB_OK;
+  }
+  GCNB_REQUIRE(G != nullptr && ldg >= N, "G is null or ldg < N");
+  const int slabs = (int)(((int64_t)K + kColsumRows - 1) / kColsumRows);
+  float* part = nullptr;
+  GCNB_CHECK_CUDA(cudaMallocAsync(&part, (size_t)slabs * N * sizeof(float), stream));
+  colsum_slab_kernel<<<slabs, 256, 0, stream>>>(G, ldg, K, N, part);
+  rc = cudaGetLastError() == cudaSuccess ? GCNB_OK : set_error(GCNB_ERR_CUDA, "colsum_slab_kernel launch failed");
+  if (rc == GCNB_OK) {
+    colsum_final_kernel<<<(N + 255) / 256, 256, 0, stream>>>(part, slabs, N, colsum);
+    if (cudaGetLastError() != cudaSuccess) rc = set_error(GCNB_ERR_CUDA, "colsum_final_kernel launch failed");
+  }
+  cudaFreeAsync(part, stream);
   return rc;
 }

@@ -139,13 +139,38 @@ class _MLP2(torch.autograd.Function):
         if ctx.needs_input_grad[3]:
             gW2 = _dw(h, g, ctx.precision)
         dpre = gemm_raw(g, W2.detach(), trans_b=True, precision=ctx.precision, mask=(bits, ctx.p))
-        if ctx.needs_input_grad[1]:
-            gW1 = _dw(X.detach(), dpre, ctx.precision)
-        if ctx.has_bias and ctx.needs_input_grad[2]:
-            gb1 = dpre.sum(dim=0)
+        if ctx.needs_input_grad[1] and ctx.has_bias and ctx.needs_input_grad[2]:
+            gW1, gb1 = dw_colsum(X.detach(), dpre, ctx.precision)    # one pass over dpre for both
+        else:
+            if ctx.needs_input_grad[1]:
+                gW1 = _dw(X.detach(), dpre, ctx.precision)
+            if ctx.has_bias and ctx.needs_input_grad[2]:
+                gb1 = dpre.sum(dim=0)
         if ctx.needs_input_grad[0]:
             gX = gemm_raw(dpre, W1.detach(), trans_b=True, precision=ctx.precision)
         return gX, gW1, gb1, gW2, None, None, None, None, None
+
+
+def dw_colsum(X, g, precision=PRECISION_3XTF32):
+    """``(Xᵀ·g, g.sum(0))`` from one pass over the two vertex-sized operands (gcnb_xw_tn_colsum): the weight and bias
+    gradients of ``X @ W + b``.  Deterministic (fixed summation order)."""
+    if not (X.is_cuda and g.is_cuda and X.dtype == torch.float32 and g.dtype == torch.float32 and X.dim() == 2
+            and g.dim() == 2 and X.shape[0] == g.shape[0]):
+        raise ValueError("gemm.dw_colsum: X [K, M] and g [K, N] must be float32 CUDA matrices over the same rows")
+    if X.stride(1) != 1:
+        X = X.contiguous()
+    if g.stride(1) != 1:
+        g = g.contiguous()
+    K, M = X.shape
+    N = g.shape[1]
+    dW = torch.empty(M, N, device=X.device, dtype=torch.float32)
+    db = torch.empty(N, device=X.device, dtype=torch.float32)
+    stream = ctypes.c_void_p(torch.cuda.current_stream(X.device).cuda_stream)
+    with torch.cuda.device(X.device):
+        _ffi.call("gcnb_xw_tn_colsum", ctypes.c_void_p(X.data_ptr()), X.stride(0), ctypes.c_void_p(g.data_ptr()),
+                  g.stride(0), ctypes.c_void_p(dW.data_ptr()), dW.stride(0), ctypes.c_void_p(db.data_ptr()), M, N, K,
+                  int(precision), stream)
+    return dW, db
 
 
 def _dw(X, g, precision):
@@ -191,6 +216,9 @@ class _XW(torch.autograd.Function):
         gX = gW = gb = None
         if ctx.needs_input_grad[0]:
             gX = gemm_raw(g, W.detach(), trans_b=True, precision=ctx.precision)      # dS · Wᵀ
+        if ctx.needs_input_grad[1] and ctx.has_bias and ctx.needs_input_grad[2]:
+            gW, gb = dw_colsum(X.detach(), g, ctx.precision)
+            return gX, gW, gb, None, None, None
         if ctx.needs_input_grad[1]:
             # Xᵀ·dS.  gcnb_xw lays its second operand out once per call (prep kernel, cost ∝ its size), so
             # the narrower of X [M×K] and dS [M×N] goes second: dW = Xᵀ·dS or (dSᵀ·X)ᵀ

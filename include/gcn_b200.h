@@ -128,6 +128,13 @@ int gcnb_xw_ex(const float* X, int64_t ldx, int trans_x, const float* W, int64_t
                float* D, int64_t ldd, int64_t M, int N, int K, const float* bias, int epilogue,
                const uint32_t* mask_in, uint32_t* mask_out, int64_t ldm, float drop_p, uint32_t seed,
                int precision, void* stream);
+/* dW = X^T·G [M x N] and db = 1^T·G [N] (the column sums of G) from ONE pass over the vertex-sized operands
+ * X [K x M] and G [K x N], both row-major over the K vertices: what autograd derives for `self.weight` and
+ * `self.bias` of `torch.mm(input, self.weight)` ... `output + self.bias` (pygcn/gcn6.py:131-143).  On the tall-K
+ * streaming kernel the sums ride along as one more row of the product (a ones column in X's tile); elsewhere
+ * they are two fixed-order passes over G.  Deterministic either way. */
+int gcnb_xw_tn_colsum(const float* X, int64_t ldx, const float* G, int64_t ldg, float* D, int64_t ldd,
+                      float* colsum, int64_t M, int N, int K, int precision, void* stream);
 int gcnb_dropout_keeps(int64_t row, int col, int N, float drop_p, uint32_t seed);
 
 /* Fused log-softmax + NLL of the GCN head (replaces F.log_softmax, pygcn/gcn6.py:248, and

@@ -224,3 +224,39 @@ def test_xw_tall_k_streaming_kernel(K, M, N, precision):
     got = gemm.gemm_raw(Xp[:, 4:4 + M], Gp[:, :N], trans_a=True, bias=b, relu=True, precision=precision)
     refp = torch.relu(Xp[:, 4:4 + M].double().t() @ Gp[:, :N].double() + b.double())
     assert rel(got, refp) < tol
+
+
+@pytest.mark.parametrize("K,M,N", [(400_000, 100, 256), (70_001, 48, 64), (50_000, 128, 64), (300_000, 256, 48),
+                                   (3_000, 100, 256), (40_000, 30, 50), (9_000, 16, 7)])
+def test_dw_colsum_one_pass(K, M, N):
+    """gcnb_xw_tn_colsum: dW = Xᵀ·G and db = 1ᵀ·G from one pass (ones column in the 128-row tile of the tall-K
+    streaming kernel when M < 128; two fixed-order passes over G otherwise — M = 128 / 256, small K, widths that
+    are not multiples of 4).  Both against fp64; repeated calls are bit-identical."""
+    g = torch.Generator(device=DEV).manual_seed(K % 997 + M + N)
+    X = torch.randn(K, M, device=DEV, generator=g)
+    G = torch.randn(K, N, device=DEV, generator=g) + 0.25      # a non-zero mean: the sums do not cancel
+    dW, db = gemm.dw_colsum(X, G)
+    tol = TOL[0] * (2 if K > 100_000 else 1)
+    assert rel(dW, X.double().t() @ G.double()) < tol
+    assert rel(db, G.double().sum(0)) < 1e-5     # north_star's fp32 tolerance; torch's own fp32 sum: ~1e-6
+    dW2, db2 = gemm.dw_colsum(X, G)
+    assert torch.equal(dW, dW2) and torch.equal(db, db2)
+    # padded leading dimensions
+    Xp = torch.randn(K, M + 8, device=DEV, generator=g)
+    Gp = torch.randn(K, N + 4, device=DEV, generator=g)
+    dW, db = gemm.dw_colsum(Xp[:, 4:4 + M], Gp[:, :N])
+    assert rel(dW, Xp[:, 4:4 + M].double().t() @ Gp[:, :N].double()) < tol
+    assert rel(db, Gp[:, :N].double().sum(0)) < 1e-5
+
+
+def test_xw_autograd_bias_gradient_one_pass():
+    """gemm.xw with a bias: weight and bias gradients come out of gcnb_xw_tn_colsum and match torch autograd."""
+    g = torch.Generator(device=DEV).manual_seed(5)
+    X = torch.randn(60_000, 100, device=DEV, generator=g)
+    W = torch.randn(100, 64, device=DEV, generator=g, requires_grad=True)
+    b = torch.randn(64, device=DEV, generator=g, requires_grad=True)
+    go = torch.randn(60_000, 64, device=DEV, generator=g)
+    gemm.xw(X, W, b).backward(go)
+    gW, gb = W.grad.clone(), b.grad.clone()
+    assert rel(gW, X.double().t() @ go.double()) < 2 * TOL[0]
+    assert rel(gb, go.double().sum(0)) < 1e-5

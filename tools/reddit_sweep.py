@@ -2,6 +2,8 @@
 identity / degree / RCM / Gorder(3) / Rabbit with the permutations cached in profiles/perm/ (host seconds in
 profiles/perm/reddit_host_seconds_r02.json), k = 128 and 602, stream class and (k = 128) the opt-in panel class.
 One graph generation (CPU generator, the one the cached permutations belong to), one JSON line per point.
+The first version of this tool recorded the start event on an idle GPU, so host time of the call landed inside
+the interval (profiles/r02_n_reddit_sweep.jsonl: up to +2 ms); it now times like bench.py.
     python tools/reddit_sweep.py [orders...]"""
 import json
 import os
@@ -24,17 +26,11 @@ print(json.dumps({"graph": "reddit-shaped", "n": n, "nnz": nnz, "generate_s": ro
 host = json.load(open(os.path.join(ROOT, "profiles", "perm", "reddit_host_seconds_r02.json")))
 
 
+import bench  # noqa: E402  (timing as in bench.py: launches queued behind a spin kernel, events on the launching stream)
+
+
 def timed(fn, reps=10):
-    for _ in range(3):
-        fn()
-    torch.cuda.synchronize()
-    ts = []
-    for _ in range(reps):
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record(); fn(); b.record(); torch.cuda.synchronize()
-        ts.append(a.elapsed_time(b))
-    ts.sort()
-    return ts[len(ts) // 2]
+    return bench._event_ms(fn, reps=reps, warm=3)
 
 
 g = torch.Generator(device=dev).manual_seed(15)
