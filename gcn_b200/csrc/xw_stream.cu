@@ -83,6 +83,8 @@ struct Params {
   uint32_t keep_thresh;      // DROPOUT: keep when the element's hash byte >= thresh (0..255)
   uint32_t seed;
   int d_vec;                 // 16-byte stores of D allowed
+  int dbg;                   // GCNB_XS_DEBUG bits (diagnosis only, results wrong): 1 MMA hi·hi only, 2 converters skip the
+                             // low part, 4 epilogue skips the global stores, 8 every X load reads tile 0 (L2 hits)
 };
 
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -233,7 +235,7 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
           asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(full), "r"((uint32_t)CHUNK_A) : "memory");
           asm volatile(
               "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-              ::"r"(smem_addr(ring + s * CHUNK_A)), "l"(&tmap_x), "r"(kc * KC), "r"((int)m0), "r"(full) : "memory");
+              ::"r"(smem_addr(ring + s * CHUNK_A)), "l"(&tmap_x), "r"(kc * KC), "r"((p.dbg & 8) ? 0 : (int)m0), "r"(full) : "memory");
         }
       }
     }
@@ -291,7 +293,7 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
             const uint32_t o = ks * 32;
             const uint32_t acc = (kc > 0 || ks > 0) ? 1u : 0u;
             mma_tf32(tmem_d, make_desc_sw128(a_raw + o), make_desc_sw128(w_hi + o), IDESC, acc);
-            if constexpr (MODE == 0) {
+            if (MODE == 0 && !(p.dbg & 1)) {
               mma_tf32(tmem_d, make_desc_sw128(a_raw + o), make_desc_sw128(w_lo + o), IDESC, 1u);
               mma_tf32(tmem_d, make_desc_sw128(a_lo + o), make_desc_sw128(w_hi + o), IDESC, 1u);
             }
@@ -318,6 +320,7 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
           mbar_wait(LOEMPTY(sl), ((it / LO) & 1) ^ 1);
           uint8_t* raw = ring + sa * CHUNK_A;
           uint8_t* lop = lo + sl * CHUNK_A;
+          if (!(p.dbg & 2))
 #pragma unroll
           for (int j = 0; j < CHUNK_A / 16 / 128; ++j) {
             const int off = (ct + j * 128) * 16;
@@ -351,13 +354,23 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
       const int64_t m0 = unit_m0(t) + q * 32;
       const int n0 = nt * BN;
       const int64_t myrow = m0 + lane;
-      mbar_wait(TFULL(buf), (tl >> 1) & 1);
-      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const uint32_t taddr0 = tmem_base + buf * BN + ((uint32_t)(q * 32) << 16);
       bool released = false;
 #pragma unroll 1
       for (int c0 = eg * 32; c0 < BN; c0 += NEG * 32) {
         if (n0 + c0 >= p.N) break;                   // warp-uniform
+        const int colb = n0 + c0;
+        const int epi = p.epi;
+        // operands of the elementwise part, requested before the accumulator is waited for (their latency — DRAM
+        // for the mask word — hides behind the tcgen05.ld): lane j holds the bias of column colb + j
+        float bias_j = 0.f;
+        if ((epi & GCNB_EPI_BIAS) && colb + lane < p.N) bias_j = __ldg(p.bias + colb + lane);
+        uint32_t min_word = 0xffffffffu;
+        if ((epi & GCNB_EPI_MASK) && myrow < p.M) min_word = p.mask_in[myrow * p.ldm + (colb >> 5)];
+        if (c0 == eg * 32) {
+          mbar_wait(TFULL(buf), (tl >> 1) & 1);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        }
         uint32_t r[32];
         asm volatile(
             "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
@@ -376,33 +389,52 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
           mbar_arrive(TEMPTY(buf));
           released = true;
         }
-        // ---- elementwise epilogue, thread = row, 32 consecutive columns in registers ----
-        const int colb = n0 + c0;
-        uint32_t min_word = 0xffffffffu;
-        if ((p.epi & GCNB_EPI_MASK) && myrow < p.M) min_word = p.mask_in[myrow * p.ldm + (colb >> 5)];
-        uint32_t out_word = 0;
+        // ---- elementwise epilogue, thread = row, 32 consecutive columns in registers.  One warp-uniform branch
+        // per PIECE, each piece a straight run over the 32 values: with the flags tested per element the loop was
+        // ~1200 predicated instructions per slice and the epilogue warps, not memory, set the pace of the kernel
+        // (profiles/r02_q_xs_debug.jsonl: 1.39 ms with loads from L2, one MMA pass and no stores) ----
+        if (epi & GCNB_EPI_BIAS) {
+          __syncwarp();
+          reinterpret_cast<float*>(my)[lane] = bias_j;            // 128 bytes of the transpose tile, before it is used
+          __syncwarp();
 #pragma unroll
-        for (int g4 = 0; g4 < 8; ++g4) {
-          uint32_t h = 0;
-          if (p.epi & GCNB_EPI_DROPOUT) h = mix32((uint64_t)myrow * (uint64_t)n4 + (uint64_t)((colb >> 2) + g4), p.seed);
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const int j = g4 * 4 + e;
-            float x = __uint_as_float(r[j]);
-            const int col = colb + j;
-            if (col < p.N) {
-              if (p.epi & GCNB_EPI_BIAS) x += __ldg(p.bias + col);
-              if (p.epi & GCNB_EPI_RELU) x = fmaxf(x, 0.f);
-              if (p.epi & GCNB_EPI_DROPOUT) x = ((h >> (8 * e)) & 0xffu) >= p.keep_thresh ? x * p.scale : 0.f;
-              if (p.epi & GCNB_EPI_MASK) x = ((min_word >> j) & 1u) ? x * p.scale : 0.f;
-              if (x > 0.f) out_word |= 1u << j;
-            } else {
-              x = 0.f;
-            }
-            r[j] = __float_as_uint(x);
+          for (int j = 0; j < 32; j += 4) {
+            const float4 b4 = *reinterpret_cast<const float4*>(my + j * 4);   // broadcast read
+            r[j] = __float_as_uint(__uint_as_float(r[j]) + b4.x);
+            r[j + 1] = __float_as_uint(__uint_as_float(r[j + 1]) + b4.y);
+            r[j + 2] = __float_as_uint(__uint_as_float(r[j + 2]) + b4.z);
+            r[j + 3] = __float_as_uint(__uint_as_float(r[j + 3]) + b4.w);
           }
         }
-        if (p.mask_out != nullptr && myrow < p.M) p.mask_out[myrow * p.ldm + (colb >> 5)] = out_word;
+        if (epi & GCNB_EPI_RELU) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(fmaxf(__uint_as_float(r[j]), 0.f));
+        }
+        if (epi & GCNB_EPI_DROPOUT) {
+          const uint64_t g0 = (uint64_t)myrow * (uint64_t)n4 + (uint64_t)(colb >> 2);
+#pragma unroll
+          for (int g4 = 0; g4 < 8; ++g4) {
+            const uint32_t h = mix32(g0 + (uint64_t)g4, p.seed);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int j = g4 * 4 + e;
+              r[j] = ((h >> (8 * e)) & 0xffu) >= p.keep_thresh ? __float_as_uint(__uint_as_float(r[j]) * p.scale) : 0u;
+            }
+          }
+        }
+        if (epi & GCNB_EPI_MASK) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            r[j] = ((min_word >> j) & 1u) ? __float_as_uint(__uint_as_float(r[j]) * p.scale) : 0u;
+        }
+        if (p.mask_out != nullptr) {
+          uint32_t out_word = 0;
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (__uint_as_float(r[j]) > 0.f) out_word |= 1u << j;
+          if (colb + 32 > p.N) out_word &= (1u << (p.N - colb)) - 1u;   // columns past N carry no bit
+          if (myrow < p.M) p.mask_out[myrow * p.ldm + (colb >> 5)] = out_word;
+        }
         // ---- transpose through the private tile: 16-byte chunks, pitch 144 (conflict-free) ----
         __syncwarp();
 #pragma unroll
@@ -412,25 +444,35 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
         // read back 4 rows x 128 bytes per instruction: full output lines
         const int ch = lane & 7;
         const int col = colb + ch * 4;
+        if (p.dbg & 4) continue;
+        if (p.d_vec && colb + 32 <= p.N && m0 + 32 <= p.M) {        // whole slice inside the matrix (warp-uniform)
+          float* dp = p.D + (m0 + (lane >> 3)) * p.ldd + col;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int rr = i * 4 + (lane >> 3);
-          const int64_t row = m0 + rr;
-          const float4 v = *reinterpret_cast<const float4*>(my + rr * STG_PITCH + ch * 16);
-          if (row < p.M && col < p.N) {
-            float* dp = p.D + row * p.ldd + col;
-            if (p.d_vec && col + 4 <= p.N) {
-              *reinterpret_cast<float4*>(dp) = v;
-            } else {
-              const float o[4] = {v.x, v.y, v.z, v.w};
+          for (int i = 0; i < 8; ++i)
+            *reinterpret_cast<float4*>(dp + (int64_t)(i * 4) * p.ldd) =
+                *reinterpret_cast<const float4*>(my + (i * 4 + (lane >> 3)) * STG_PITCH + ch * 16);
+        } else {
 #pragma unroll
-              for (int e = 0; e < 4; ++e)
-                if (col + e < p.N) dp[e] = o[e];
+          for (int i = 0; i < 8; ++i) {
+            const int rr = i * 4 + (lane >> 3);
+            const int64_t row = m0 + rr;
+            const float4 v = *reinterpret_cast<const float4*>(my + rr * STG_PITCH + ch * 16);
+            if (row < p.M && col < p.N) {
+              float* dp = p.D + row * p.ldd + col;
+              if (p.d_vec && col + 4 <= p.N) {
+                *reinterpret_cast<float4*>(dp) = v;
+              } else {
+                const float o[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e)
+                  if (col + e < p.N) dp[e] = o[e];
+              }
             }
           }
         }
       }
       if (!released) {   // this warp had no column group in the tile (N small): still a party of the barrier
+        mbar_wait(TFULL(buf), (tl >> 1) & 1);
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         mbar_arrive(TEMPTY(buf));
       }
@@ -564,6 +606,8 @@ int xw_stream_run(const float* X, int64_t ldx, const float* W, int64_t ldw, int 
   p.scale = (epi & (GCNB_EPI_DROPOUT | GCNB_EPI_MASK)) ? 256.f / (256.f - (float)p.keep_thresh) : 1.f;
   p.seed = seed;
   p.d_vec = (((uintptr_t)D & 15) == 0) && (ldd % 4 == 0) && (N % 4 == 0);
+  static const int dbg_env = getenv("GCNB_XS_DEBUG") ? atoi(getenv("GCNB_XS_DEBUG")) : 0;
+  p.dbg = dbg_env;
   int grid;
   if (wres) {
     p.groups = (int)std::max<int64_t>(1, std::min<int64_t>(p.mtiles, n_sm / ntiles));

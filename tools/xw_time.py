@@ -61,7 +61,10 @@ if os.environ.get("XW_TIME_VARIANTS"):
         ("copy h -> dpre (2.5 GB in, 2.5 GB out)", lambda: dpre.copy_(h), 8 * n * 256),
         ("fill dpre (2.5 GB out)", lambda: dpre.fill_(1.0), 4 * n * 256),
     ]
+only = os.environ.get("XW_TIME_ONLY")   # substring filter on the product names
 for name, fn, nbytes in cases:
+    if only and only not in name:
+        continue
     ms = timed(fn)
     print(json.dumps({"product": name, "ms": round(ms, 4), "GB": round(nbytes / 1e9, 3), "GBps": round(nbytes / ms / 1e6, 1),
                       "env": {k: v for k, v in os.environ.items() if k.startswith("GCNB_X")}}), flush=True)
