@@ -17,9 +17,9 @@
 //   warp 1      MMA issuer (one elected thread): tcgen05.mma kind::tf32, A and B from shared memory,
 //               accumulator in TMEM, two accumulator buffers so the epilogue of tile i overlaps the MMAs of
 //               tile i+1; tcgen05.commit frees the rings / publishes the accumulator
-//   warps 4-7   converters: only the LOW part of the 3xTF32 split is computed, lo = tf32(x - trunc13(x)),
+//   warps 4-11  converters: only the LOW part of the 3xTF32 split is computed, lo = tf32(x - trunc13(x)),
 //               into a small ring; the HIGH part is the raw fp32 word with its 13 low mantissa bits cleared
-//   warps 8-15  epilogue (8-11 when BN = 64): tcgen05.ld, bias / ReLU / dropout / mask with thread = row,
+//   warps 12-19 epilogue: tcgen05.ld, bias / ReLU / dropout / mask with thread = row,
 //               one 32-bit word of mask bits per 32 outputs, then a transpose through a private
 //               shared-memory tile so that every store instruction writes full 128-byte lines
 //   * x·w = hi_x·hi_w + hi_x·lo_w + lo_x·hi_w (three MMAs per k-step of 8), error ~1e-6 of fp32 like the
@@ -33,6 +33,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdio.h>
 #include <stdlib.h>
 
 #include <algorithm>
@@ -51,12 +52,14 @@ constexpr int STG_BYTES = 32 * STG_PITCH;
 constexpr int SMEM_MAX = 232448; // 227 KB of dynamic shared memory per CTA
 
 constexpr int NE = 8;            // epilogue warps (two per TMEM lane quadrant)
-constexpr int THREADS = (8 + NE) * 32;
+constexpr int NCV = 8;           // converter warps
+constexpr int THREADS = (4 + NCV + NE) * 32;
 constexpr int RA_MAX = 12;       // most X chunks in flight (barrier slots)
 __host__ __device__ constexpr int w_chunk(int bn) { return 2 * bn * 128; }      // hi | lo
 // shared memory: X ring (ra chunks) | lo ring (2) | W (w_slots chunks: 2 when streamed, nkc when resident) |
 // epilogue transpose tiles | barriers; + 1 KB alignment slack
 constexpr int LO_MAX = 4;        // most low-part chunks in flight
+constexpr int kTraceLen = 512;
 __host__ __device__ constexpr int fixed_bytes(int bn, int w_slots, int lo_slots) {
   return w_slots * w_chunk(bn) + lo_slots * CHUNK_A + NE * STG_BYTES + 1024 /* barriers */ + 1024 /* alignment */;
 }
@@ -83,6 +86,7 @@ struct Params {
   uint32_t keep_thresh;      // DROPOUT: keep when the element's hash byte >= thresh (0..255)
   uint32_t seed;
   int d_vec;                 // 16-byte stores of D allowed
+  unsigned long long* trace; // GCNB_XS_TRACE: clock64() stamps of CTA 0, [8 roles][kTraceLen], diagnosis only
   int dbg;                   // GCNB_XS_DEBUG bits (diagnosis only, results wrong): 1 MMA hi·hi only, 2 converters skip the
                              // low part, 4 epilogue skips the global stores, 8 every X load reads tile 0 (L2 hits)
 };
@@ -125,6 +129,11 @@ __device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t da, uint64_t 
 }
 __device__ __forceinline__ void commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ bool elect_one() {   // one lane of a converged warp
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
 }
 __device__ __forceinline__ uint32_t to_tf32(float x) {
   uint32_t r;
@@ -199,7 +208,7 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(EMPTYA(s)));
     }
     for (int b = 0; b < LO_MAX; ++b) {
-      asm volatile("mbarrier.init.shared::cta.b64 [%0], 128;" ::"r"(CONV(b)));
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(CONV(b)), "r"(NCV * 32));
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(LOEMPTY(b)));
     }
     for (int b = 0; b < 2; ++b) {
@@ -219,6 +228,9 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = *tmem_slot;
+  auto stamp = [&](int role, uint32_t idx) {
+    if (p.trace != nullptr && blockIdx.x == 0 && idx < (uint32_t)kTraceLen) p.trace[role * kTraceLen + idx] = (unsigned long long)clock64();
+  };
 
   if (warp == 0) {
     // ---------------- X producer: one TMA tensor-map load per k-chunk ----------------
@@ -236,6 +248,7 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
           asm volatile(
               "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
               ::"r"(smem_addr(ring + s * CHUNK_A)), "l"(&tmap_x), "r"(kc * KC), "r"((p.dbg & 8) ? 0 : (int)m0), "r"(full) : "memory");
+          stamp(0, it);
         }
       }
     }
@@ -270,7 +283,11 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
     }
   } else if (warp == 1) {
     // ---------------- MMA issuer ----------------
-    if (lane == 0) {
+    // The whole warp walks the loop (uniform control flow, operands in uniform registers) and one elected lane
+    // issues.  Under `if (lane == 0)` the compiler wraps every tcgen05.mma in a uniformising loop (ELECT, five
+    // R2UR.BROADCAST, BRA.U.ANY): ~85 cycles per MMA, 1000 per chunk — as long as the chunk's load or conversion
+    // (clock64 timeline of the roles, profiles/r02_t_xs_trace_report.txt).
+    {
       uint32_t it = 0, tl = 0;
       if constexpr (WRES) {
         if (u0 < uend) mbar_wait(FULLW(0), 0);
@@ -278,7 +295,6 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
       for (int64_t t = u0; t < uend; t += ustep, ++tl) {
         const uint32_t buf = tl & 1;
         mbar_wait(TEMPTY(buf), ((tl >> 1) & 1) ^ 1);       // the epilogue has drained this accumulator
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const uint32_t tmem_d = tmem_base + buf * BN;
         for (int kc = 0; kc < p.nkc; ++kc, ++it) {
           const int sa = it % RA, sw = it & 1, sl = it % LO;
@@ -286,44 +302,57 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
           if constexpr (!WRES) mbar_wait(FULLW(sw), (it >> 1) & 1);
           mbar_wait(CONV(sl), (it / LO) & 1);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          if (lane == 0) stamp(4, it);
           const uint32_t a_raw = smem_addr(ring + sa * CHUNK_A), a_lo = smem_addr(lo + sl * CHUNK_A);
           const uint32_t w_hi = smem_addr(wbuf + (WRES ? kc : sw) * W_CHUNK), w_lo = w_hi + BN * 128;
+          // k-steps of 8 that hold columns < K (the tail chunk of K = 100 has one, not four; the TMA unit zero-fills
+          // the columns past K inside it)
+          const int ksteps = min(KC / 8, (p.K - kc * KC + 7) >> 3);
+          __syncwarp();
+          if (elect_one()) {
 #pragma unroll
-          for (int ks = 0; ks < KC / 8; ++ks) {     // K = 8 tf32 = 32 bytes per MMA: advance inside the swizzle row
-            const uint32_t o = ks * 32;
-            const uint32_t acc = (kc > 0 || ks > 0) ? 1u : 0u;
-            mma_tf32(tmem_d, make_desc_sw128(a_raw + o), make_desc_sw128(w_hi + o), IDESC, acc);
-            if (MODE == 0 && !(p.dbg & 1)) {
-              mma_tf32(tmem_d, make_desc_sw128(a_raw + o), make_desc_sw128(w_lo + o), IDESC, 1u);
-              mma_tf32(tmem_d, make_desc_sw128(a_lo + o), make_desc_sw128(w_hi + o), IDESC, 1u);
+            for (int ks = 0; ks < KC / 8; ++ks) {     // K = 8 tf32 = 32 bytes per MMA: advance inside the swizzle row
+              if (ks < ksteps) {
+                const uint32_t o = ks * 32;
+                const uint32_t acc = (kc > 0 || ks > 0) ? 1u : 0u;
+                mma_tf32(tmem_d, make_desc_sw128(a_raw + o), make_desc_sw128(w_hi + o), IDESC, acc);
+                if (MODE == 0 && !(p.dbg & 1)) {
+                  mma_tf32(tmem_d, make_desc_sw128(a_raw + o), make_desc_sw128(w_lo + o), IDESC, 1u);
+                  mma_tf32(tmem_d, make_desc_sw128(a_lo + o), make_desc_sw128(w_hi + o), IDESC, 1u);
+                }
+              }
             }
+            commit(EMPTYA(sa));                        // ring slots reusable once these MMAs have read them
+            if constexpr (!WRES) commit(EMPTYW(sw));
+            commit(LOEMPTY(sl));
+            if (kc == p.nkc - 1) commit(TFULL(buf));   // accumulator complete
           }
-          commit(EMPTYA(sa));                        // ring slots reusable once these MMAs have read them
-          if constexpr (!WRES) commit(EMPTYW(sw));
-          commit(LOEMPTY(sl));
+          __syncwarp();
+          if (lane == 0) stamp(5, it);
         }
-        commit(TFULL(buf));                          // accumulator complete
       }
     }
-  } else if (warp >= 4 && warp < 8) {
+  } else if (warp >= 4 && warp < 4 + NCV) {
     // ---------------- converters: lo = tf32(x - trunc13(x)) on the physical (swizzled) layout ----------------
     // The high part is written back truncated, so that it does not matter whether the tensor core truncates or
     // rounds the 13 low mantissa bits of an fp32 word it is handed as tf32 (fence.proxy.async publishes the generic
     // stores to the tensor core's proxy).  Single-pass mode: the same without the low part.
     {
-      const int ct = tid - 128;                      // 0..127
+      const int ct = tid - 128;                      // 0 .. NCV*32-1
       uint32_t it = 0;
       for (int64_t t = u0; t < uend; t += ustep) {
         for (int kc = 0; kc < p.nkc; ++kc, ++it) {
           const int sa = it % RA, sl = it % LO;
           mbar_wait(FULLA(sa), (it / RA) & 1);
+          if (ct == 0) stamp(1, it);
           mbar_wait(LOEMPTY(sl), ((it / LO) & 1) ^ 1);
+          if (ct == 0) stamp(2, it);
           uint8_t* raw = ring + sa * CHUNK_A;
           uint8_t* lop = lo + sl * CHUNK_A;
           if (!(p.dbg & 2))
 #pragma unroll
-          for (int j = 0; j < CHUNK_A / 16 / 128; ++j) {
-            const int off = (ct + j * 128) * 16;
+          for (int j = 0; j < CHUNK_A / 16 / (NCV * 32); ++j) {
+            const int off = (ct + j * NCV * 32) * 16;
             const uint4 v = *reinterpret_cast<const uint4*>(raw + off);
             if constexpr (MODE == 0) {
               uint4 o;
@@ -338,14 +367,15 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
           }
           asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic stores -> tensor core's proxy
           mbar_arrive(CONV(sl));
+          if (ct == 0) stamp(3, it);
         }
       }
     }
-  } else if (warp >= 8) {
+  } else if (warp >= 4 + NCV) {
     // ---------------- epilogue ----------------
     const int q = warp & 3;                          // TMEM lanes 32q .. 32q+31 belong to this warp
-    const int eg = (warp - 8) >> 2;                  // which of the NEG warps of this quadrant
-    uint8_t* my = stg + (warp - 8) * STG_BYTES;
+    const int eg = (warp - 4 - NCV) >> 2;            // which of the NEG warps of this quadrant
+    uint8_t* my = stg + (warp - 4 - NCV) * STG_BYTES;
     const int64_t n4 = (p.N + 3) / 4;                // dropout hash groups per row
     uint32_t tl = 0;
     for (int64_t t = u0; t < uend; t += ustep, ++tl) {
@@ -370,6 +400,7 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
         if (c0 == eg * 32) {
           mbar_wait(TFULL(buf), (tl >> 1) & 1);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          if (warp == 4 + NCV && lane == 0) stamp(6, tl);
         }
         uint32_t r[32];
         asm volatile(
@@ -471,6 +502,7 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
           }
         }
       }
+      if (warp == 4 + NCV && lane == 0) stamp(7, tl);
       if (!released) {   // this warp had no column group in the tile (N small): still a party of the barrier
         mbar_wait(TFULL(buf), (tl >> 1) & 1);
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -608,6 +640,15 @@ int xw_stream_run(const float* X, int64_t ldx, const float* W, int64_t ldw, int 
   p.d_vec = (((uintptr_t)D & 15) == 0) && (ldd % 4 == 0) && (N % 4 == 0);
   static const int dbg_env = getenv("GCNB_XS_DEBUG") ? atoi(getenv("GCNB_XS_DEBUG")) : 0;
   p.dbg = dbg_env;
+  // GCNB_XS_TRACE=<file>: clock64() stamps of CTA 0's roles (producer issue, converter waits / arrive, MMA issue /
+  // commit, epilogue start / end) for the first kTraceLen chunks / tiles, appended to <file> after a device
+  // synchronisation.  Diagnosis only (tools/README.md).
+  static const char* trace_path = getenv("GCNB_XS_TRACE");
+  p.trace = nullptr;
+  if (trace_path) {
+    GCNB_CHECK_CUDA(cudaMalloc(&p.trace, 8 * xs::kTraceLen * sizeof(unsigned long long)));
+    GCNB_CHECK_CUDA(cudaMemset(p.trace, 0, 8 * xs::kTraceLen * sizeof(unsigned long long)));
+  }
   int grid;
   if (wres) {
     p.groups = (int)std::max<int64_t>(1, std::min<int64_t>(p.mtiles, n_sm / ntiles));
@@ -619,6 +660,23 @@ int xw_stream_run(const float* X, int64_t ldx, const float* W, int64_t ldw, int 
   const int rc = precision == 0 ? xs_dispatch<0>(bn, wres, tmap, p, grid, smem, stream)
                                 : xs_dispatch<1>(bn, wres, tmap, p, grid, smem, stream);
   cudaFreeAsync(img, stream);
+  if (p.trace) {
+    static unsigned long long host[8 * xs::kTraceLen];
+    if (cudaDeviceSynchronize() == cudaSuccess &&
+        cudaMemcpy(host, p.trace, sizeof(host), cudaMemcpyDeviceToHost) == cudaSuccess) {
+      if (FILE* f = fopen(trace_path, "a")) {
+        fprintf(f, "# M=%lld N=%d K=%d bn=%d wres=%d nkc=%d ra=%d lo=%d dbg=%d precision=%d\n", (long long)M, N, K, bn, (int)wres, nkc, ra,
+                lo_slots, p.dbg, precision);
+        for (int r = 0; r < 8; ++r) {
+          fprintf(f, "%d", r);
+          for (int i = 0; i < xs::kTraceLen; ++i) fprintf(f, " %llu", host[r * xs::kTraceLen + i]);
+          fprintf(f, "\n");
+        }
+        fclose(f);
+      }
+    }
+    cudaFree(p.trace);
+  }
   return rc;
 }
 

@@ -116,6 +116,11 @@ __device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t da, uint64_t 
 __device__ __forceinline__ void commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
+__device__ __forceinline__ bool elect_one() {   // one lane of a converged warp
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ uint32_t to_tf32(float x) {
   uint32_t r;
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
@@ -211,34 +216,37 @@ xt_kernel(const Params p) {
       }
     }
   } else if (warp == 1) {
-    // ---------------- MMA issuer ----------------
-    if (lane == 0) {
+    // ---------------- MMA issuer: the whole warp walks the loop (uniform control flow, descriptors in uniform
+    // registers), one elected lane issues — under `if (lane == 0)` every tcgen05.mma is wrapped in a uniformising
+    // loop of ~17 instructions (xw_stream.cu) ----------------
+    {
       const uint32_t idesc = make_idesc(n_umma);
       for (int it = 0; it < nst; ++it) {
         const int grp = it / p.chain, pos = it - grp * p.chain;
         const uint32_t buf = grp & 1;
-        if (pos == 0) {
-          mbar_wait(TEMPTY(buf), ((grp >> 1) & 1) ^ 1);
-          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        }
+        if (pos == 0) mbar_wait(TEMPTY(buf), ((grp >> 1) & 1) ^ 1);
         const uint32_t tmem_d = tmem_base + buf * 256;
         const int cs = it % CS;
         mbar_wait(CONV(cs), (it / CS) & 1);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const uint32_t a_hi = smem_addr(conv + cs * CONV_STAGE), b_hi = a_hi + A_BLOCKS * BLK;
         const uint32_t a_lo = a_hi + PART, b_lo = a_lo + A_BLOCKS * BLK;
+        __syncwarp();
+        if (elect_one()) {
 #pragma unroll
-        for (int ks = 0; ks < KV / 8; ++ks) {        // 8 vertices per MMA: two 4-row k-atoms of every block
-          const uint32_t o = ks * 1024;
-          const uint32_t acc = (pos > 0 || ks > 0) ? 1u : 0u;
-          mma_tf32(tmem_d, make_desc_mn(a_hi + o, BLK), make_desc_mn(b_hi + o, BLK), idesc, acc);
-          if constexpr (MODE == 0) {
-            mma_tf32(tmem_d, make_desc_mn(a_hi + o, BLK), make_desc_mn(b_lo + o, BLK), idesc, 1u);
-            mma_tf32(tmem_d, make_desc_mn(a_lo + o, BLK), make_desc_mn(b_hi + o, BLK), idesc, 1u);
+          for (int ks = 0; ks < KV / 8; ++ks) {        // 8 vertices per MMA: two 4-row k-atoms of every block
+            const uint32_t o = ks * 1024;
+            const uint32_t acc = (pos > 0 || ks > 0) ? 1u : 0u;
+            mma_tf32(tmem_d, make_desc_mn(a_hi + o, BLK), make_desc_mn(b_hi + o, BLK), idesc, acc);
+            if constexpr (MODE == 0) {
+              mma_tf32(tmem_d, make_desc_mn(a_hi + o, BLK), make_desc_mn(b_lo + o, BLK), idesc, 1u);
+              mma_tf32(tmem_d, make_desc_mn(a_lo + o, BLK), make_desc_mn(b_hi + o, BLK), idesc, 1u);
+            }
           }
+          commit(CEMPTY(cs));
+          if (pos == p.chain - 1 || it == nst - 1) commit(TFULL(buf));
         }
-        commit(CEMPTY(cs));
-        if (pos == p.chain - 1 || it == nst - 1) commit(TFULL(buf));
+        __syncwarp();
       }
     }
   } else if (warp >= 4 && warp < 4 + NC) {
