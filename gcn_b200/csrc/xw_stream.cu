@@ -7,20 +7,22 @@
 // Why a second kernel next to xw_tcgen05.cu: that one (one 4-warp CTA per 128 x BN tile, k-blocks of 16,
 // every fp32 value converted to tf32 hi/lo by the same threads that wait for it, a CTA-wide barrier per
 // k-block, per-thread row stores) ran at ~27 % of the HBM time of these shapes.
-// Here one CTA per SM loops over its 128-row tiles, with fixed warp roles and separate rings per stream:
+// Here one CTA per SM loops over its 128-row tiles, 20 warps with fixed roles and separate rings per stream:
 //   warp 0      X producer: one TMA tensor-map load per k-chunk (128 rows x 32 floats, SWIZZLE_128B, rows past M
-//               and columns past K zero-filled by the TMA unit) into a deep ring.  Measured on the way here:
-//               staging X, lo(X) and W in one ring leaves 32-64 KB of X in flight (profiles/r02_d_*); 16-byte
-//               cp.async copies by four loader warps instead of the TMA load are slower (r02_k_xw_shapes.jsonl)
+//               and columns past K zero-filled by the TMA unit) into a ring that takes all shared memory left
+//               (3-9 chunks).  One producer thread streams at the HBM rate this way once >= 64 KB are in flight
+//               (tools/tma_stream_probe.cu); 16-byte cp.async copies by four loader warps were slower
 //   warp 2      W producer: TMA bulk copies of the prepared W chunks (hi | lo images, L2-resident), once per CTA
-//               when they fit 64 KB, else through a ring of 2
-//   warp 1      MMA issuer (one elected thread): tcgen05.mma kind::tf32, A and B from shared memory,
-//               accumulator in TMEM, two accumulator buffers so the epilogue of tile i overlaps the MMAs of
-//               tile i+1; tcgen05.commit frees the rings / publishes the accumulator
-//   warps 4-11  converters: only the LOW part of the 3xTF32 split is computed, lo = tf32(x - trunc13(x)),
-//               into a small ring; the HIGH part is the raw fp32 word with its 13 low mantissa bits cleared
-//   warps 12-19 epilogue: tcgen05.ld, bias / ReLU / dropout / mask with thread = row,
-//               one 32-bit word of mask bits per 32 outputs, then a transpose through a private
+//               when they fit (128 KB for a 128-column tile, 64 KB for a 64-column one), else through a ring of 2
+//   warps 4-11  converters: split every raw chunk into hi (the fp32 word with its 13 low mantissa bits cleared) and
+//               lo = tf32(x - hi) and write both into TENSOR memory (tcgen05.st, thread = row): the MMA takes its
+//               A operand from there, only W comes from shared memory
+//   warp 1      MMA issuer: the whole warp walks the loop, one elected lane issues tcgen05.mma kind::tf32 (A from
+//               tensor memory, B = W from shared memory), accumulator in TMEM, two accumulator buffers so the
+//               epilogue of tile i overlaps the MMAs of tile i+1; tcgen05.commit frees the rings / publishes the
+//               accumulator
+//   warps 12-19 epilogue: tcgen05.ld, bias / ReLU / dropout / mask with thread = row (one warp-uniform branch per
+//               piece), one 32-bit word of mask bits per 32 outputs, then a transpose through a private
 //               shared-memory tile so that every store instruction writes full 128-byte lines
 //   * x·w = hi_x·hi_w + hi_x·lo_w + lo_x·hi_w (three MMAs per k-step of 8), error ~1e-6 of fp32 like the
 //     first kernel (W is split with round-to-nearest by the prep kernel; |lo_x·lo_w| <= 2^-21 |x·w|).
@@ -56,16 +58,18 @@ constexpr int NCV = 8;           // converter warps
 constexpr int THREADS = (4 + NCV + NE) * 32;
 constexpr int RA_MAX = 12;       // most X chunks in flight (barrier slots)
 __host__ __device__ constexpr int w_chunk(int bn) { return 2 * bn * 128; }      // hi | lo
-// shared memory: X ring (ra chunks) | lo ring (2) | W (w_slots chunks: 2 when streamed, nkc when resident) |
+// shared memory: X ring (ra chunks) | W (w_slots chunks: 2 when streamed, nkc when resident) |
 // epilogue transpose tiles | barriers; + 1 KB alignment slack
-constexpr int LO_MAX = 4;        // most low-part chunks in flight
+// tensor memory (512 columns): two accumulators of BN columns | ring of NA converted X chunks, 64 columns each
+// (hi: 32 k-values | lo: 32)
+constexpr int NA_MAX = 4;        // most converted chunks in flight
+constexpr int A_COLS = 2 * KC;   // TMEM columns of one converted chunk
 constexpr int kTraceLen = 512;
-__host__ __device__ constexpr int fixed_bytes(int bn, int w_slots, int lo_slots) {
-  return w_slots * w_chunk(bn) + lo_slots * CHUNK_A + NE * STG_BYTES + 1024 /* barriers */ + 1024 /* alignment */;
+__host__ __device__ constexpr int fixed_bytes(int bn, int w_slots) {
+  return w_slots * w_chunk(bn) + NE * STG_BYTES + 1024 /* barriers */ + 1024 /* alignment */;
 }
-__host__ __device__ constexpr int ring_a(int bn, int w_slots, int lo_slots) {
-  return (SMEM_MAX - fixed_bytes(bn, w_slots, lo_slots)) / CHUNK_A < RA_MAX
-             ? (SMEM_MAX - fixed_bytes(bn, w_slots, lo_slots)) / CHUNK_A : RA_MAX;
+__host__ __device__ constexpr int ring_a(int bn, int w_slots) {
+  return (SMEM_MAX - fixed_bytes(bn, w_slots)) / CHUNK_A < RA_MAX ? (SMEM_MAX - fixed_bytes(bn, w_slots)) / CHUNK_A : RA_MAX;
 }
 
 struct Params {
@@ -78,7 +82,7 @@ struct Params {
   int64_t M; int N; int K;
   int nkc, ntiles;
   int ra;                    // X chunks in flight (ring slots)
-  int lo;                    // low-part chunks in flight (2..LO_MAX)
+  int na;                    // converted chunks in flight in tensor memory (2..NA_MAX)
   int groups;                // resident-W mode: CTAs per n-tile (CTA b works on n-tile b % ntiles, m-tiles b / ntiles + i * groups)
   int64_t mtiles;
   int epi;
@@ -127,6 +131,19 @@ __device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t da, uint64_t 
       "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
       ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
 }
+// A operand in tensor memory (lane = row, one 32-bit column per k), B from shared memory
+__device__ __forceinline__ void mma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t db, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "r"(tmem_a), "l"(db), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* v) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+      ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]),
+        "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]) : "memory");
+}
 __device__ __forceinline__ void commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
@@ -170,17 +187,16 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
   constexpr int NEG = NE / 4;                     // epilogue warps per TMEM lane quadrant
   constexpr int W_CHUNK = w_chunk(BN);
   constexpr uint32_t IDESC = make_idesc(BN);
-  constexpr int TMEM_COLS = 2 * BN;               // two accumulator buffers (128 / 256 columns)
+  constexpr int TMEM_COLS = 512;                  // two accumulator buffers (2 x BN columns) + the converted X chunks
   const int w_slots = WRES ? p.nkc : 2;
   // 1024-byte alignment (of the shared-space address) for the 128-byte swizzle atoms
   uint8_t* smem = smem_raw + ((1024u - (smem_addr(smem_raw) & 1023u)) & 1023u);
   uint8_t* ring = smem;                            // RA x 16 KB raw X chunks
-  uint8_t* lo = ring + RA * CHUNK_A;               // 2 x 16 KB low parts
-  const int LO = p.lo;
-  uint8_t* wbuf = lo + LO * CHUNK_A;               // W chunks
+  const int NA = p.na;
+  uint8_t* wbuf = ring + RA * CHUNK_A;             // W chunks
   uint8_t* stg = wbuf + w_slots * W_CHUNK;         // NE transpose tiles
   uint64_t* bars = reinterpret_cast<uint64_t*>(stg + NE * STG_BYTES);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * RA_MAX + 8 + 2 * LO_MAX);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * RA_MAX + 8 + 2 * NA_MAX);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t bar0 = smem_addr(bars);
@@ -191,7 +207,7 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
   auto TFULL = [&](int b) { return bar0 + 8u * (uint32_t)(2 * RA_MAX + 4 + b); };
   auto TEMPTY = [&](int b) { return bar0 + 8u * (uint32_t)(2 * RA_MAX + 6 + b); };
   auto CONV = [&](int s) { return bar0 + 8u * (uint32_t)(2 * RA_MAX + 8 + s); };
-  auto LOEMPTY = [&](int s) { return bar0 + 8u * (uint32_t)(2 * RA_MAX + 8 + LO_MAX + s); };
+  auto AEMPTY = [&](int s) { return bar0 + 8u * (uint32_t)(2 * RA_MAX + 8 + NA_MAX + s); };
   // work of this CTA: units u = u0, u0 + ustep, ... of (m-tile, n-tile) pairs
   //   streamed W: unit index t over all pairs, n-tile fastest;   resident W: fixed n-tile, m-tiles of its group
   const int64_t n_tiles = p.mtiles * p.ntiles;
@@ -205,11 +221,11 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
   if (tid == 0) {
     for (int s = 0; s < RA_MAX; ++s) {
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(FULLA(s)));
-      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(EMPTYA(s)));
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(EMPTYA(s)), "r"(NCV * 32));
     }
-    for (int b = 0; b < LO_MAX; ++b) {
+    for (int b = 0; b < NA_MAX; ++b) {
       asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(CONV(b)), "r"(NCV * 32));
-      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(LOEMPTY(b)));
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(AEMPTY(b)));
     }
     for (int b = 0; b < 2; ++b) {
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(FULLW(b)));
@@ -238,17 +254,19 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
     // leading dimension — and were slower: layer-1 product 2.72 vs 2.43 ms, profiles/r02_k_xw_shapes.jsonl.)
     if (lane == 0) {
       uint32_t it = 0;
+      int s = 0;                // ring position and phase kept as counters: an integer division per chunk is a few
+      uint32_t ph = 0;          // dozen dependent instructions of a single warp, i.e. hundreds of cycles
       for (int64_t t = u0; t < uend; t += ustep) {
         const int64_t m0 = unit_m0(t);
         for (int kc = 0; kc < p.nkc; ++kc, ++it) {
-          const int s = it % RA;
-          mbar_wait(EMPTYA(s), ((it / RA) & 1) ^ 1);
+          mbar_wait(EMPTYA(s), ph ^ 1);
           const uint32_t full = FULLA(s);
           asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(full), "r"((uint32_t)CHUNK_A) : "memory");
           asm volatile(
               "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
               ::"r"(smem_addr(ring + s * CHUNK_A)), "l"(&tmap_x), "r"(kc * KC), "r"((p.dbg & 8) ? 0 : (int)m0), "r"(full) : "memory");
           stamp(0, it);
+          if (++s == RA) { s = 0; ph ^= 1; }
         }
       }
     }
@@ -288,7 +306,14 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
     // R2UR.BROADCAST, BRA.U.ANY): ~85 cycles per MMA, 1000 per chunk — as long as the chunk's load or conversion
     // (clock64 timeline of the roles, profiles/r02_t_xs_trace_report.txt).
     {
+      // This warp's own instruction stream is what the tensor pipe waits for (a single warp retires a dependent
+      // instruction every ~4+ cycles): ring positions are counters, the W descriptors are one add away from a base
+      // descriptor (16-byte units in the low word), nothing is recomputed per MMA (profiles/r02_w_xs_trace_report.txt:
+      // ~1000 cycles per chunk of 10 MMAs before this).
       uint32_t it = 0, tl = 0;
+      int sn = 0;
+      uint32_t ph_n = 0;
+      const uint64_t dw0 = make_desc_sw128(smem_addr(wbuf));
       if constexpr (WRES) {
         if (u0 < uend) mbar_wait(FULLW(0), 0);
       }
@@ -297,77 +322,85 @@ xs_kernel(const __grid_constant__ CUtensorMap tmap_x, const Params p) {
         mbar_wait(TEMPTY(buf), ((tl >> 1) & 1) ^ 1);       // the epilogue has drained this accumulator
         const uint32_t tmem_d = tmem_base + buf * BN;
         for (int kc = 0; kc < p.nkc; ++kc, ++it) {
-          const int sa = it % RA, sw = it & 1, sl = it % LO;
-          mbar_wait(FULLA(sa), (it / RA) & 1);
+          const int sw = it & 1;
+          if (lane == 0) stamp(1, it);
           if constexpr (!WRES) mbar_wait(FULLW(sw), (it >> 1) & 1);
-          mbar_wait(CONV(sl), (it / LO) & 1);
+          mbar_wait(CONV(sn), ph_n);                   // the converters have put hi | lo of this chunk into tensor memory
+          if (lane == 0) stamp(2, it);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           if (lane == 0) stamp(4, it);
-          const uint32_t a_raw = smem_addr(ring + sa * CHUNK_A), a_lo = smem_addr(lo + sl * CHUNK_A);
-          const uint32_t w_hi = smem_addr(wbuf + (WRES ? kc : sw) * W_CHUNK), w_lo = w_hi + BN * 128;
+          const uint32_t a_hi = tmem_base + 2 * BN + sn * A_COLS, a_lo = a_hi + KC;
+          const uint64_t d_hi = dw0 + (uint64_t)((WRES ? kc : sw) * (W_CHUNK >> 4)), d_lo = d_hi + (uint64_t)((BN * 128) >> 4);
           // k-steps of 8 that hold columns < K (the tail chunk of K = 100 has one, not four; the TMA unit zero-fills
           // the columns past K inside it)
           const int ksteps = min(KC / 8, (p.K - kc * KC + 7) >> 3);
           __syncwarp();
           if (elect_one()) {
 #pragma unroll
-            for (int ks = 0; ks < KC / 8; ++ks) {     // K = 8 tf32 = 32 bytes per MMA: advance inside the swizzle row
+            for (int ks = 0; ks < KC / 8; ++ks) {     // K = 8 tf32 per MMA: 8 TMEM columns of A, 32 bytes of W's swizzle row
               if (ks < ksteps) {
-                const uint32_t o = ks * 32;
                 const uint32_t acc = (kc > 0 || ks > 0) ? 1u : 0u;
-                mma_tf32(tmem_d, make_desc_sw128(a_raw + o), make_desc_sw128(w_hi + o), IDESC, acc);
+                mma_tf32_ts(tmem_d, a_hi + ks * 8, d_hi + (uint64_t)(ks * 2), IDESC, acc);
                 if (MODE == 0 && !(p.dbg & 1)) {
-                  mma_tf32(tmem_d, make_desc_sw128(a_raw + o), make_desc_sw128(w_lo + o), IDESC, 1u);
-                  mma_tf32(tmem_d, make_desc_sw128(a_lo + o), make_desc_sw128(w_hi + o), IDESC, 1u);
+                  mma_tf32_ts(tmem_d, a_hi + ks * 8, d_lo + (uint64_t)(ks * 2), IDESC, 1u);
+                  mma_tf32_ts(tmem_d, a_lo + ks * 8, d_hi + (uint64_t)(ks * 2), IDESC, 1u);
                 }
               }
             }
-            commit(EMPTYA(sa));                        // ring slots reusable once these MMAs have read them
             if constexpr (!WRES) commit(EMPTYW(sw));
-            commit(LOEMPTY(sl));
+            commit(AEMPTY(sn));                        // the chunk's TMEM columns are free once these MMAs have read them
             if (kc == p.nkc - 1) commit(TFULL(buf));   // accumulator complete
           }
           __syncwarp();
           if (lane == 0) stamp(5, it);
+          if (++sn == NA) { sn = 0; ph_n ^= 1; }
         }
       }
     }
   } else if (warp >= 4 && warp < 4 + NCV) {
-    // ---------------- converters: lo = tf32(x - trunc13(x)) on the physical (swizzled) layout ----------------
-    // The high part is written back truncated, so that it does not matter whether the tensor core truncates or
-    // rounds the 13 low mantissa bits of an fp32 word it is handed as tf32 (fence.proxy.async publishes the generic
-    // stores to the tensor core's proxy).  Single-pass mode: the same without the low part.
+    // ---------------- converters: raw fp32 chunk in shared memory -> hi | lo in TENSOR memory ----------------
+    // hi = the fp32 word with its 13 low mantissa bits cleared, lo = tf32(x - hi); thread = row (TMEM lane), two
+    // warps per lane quadrant, 16 of the chunk's 32 k-values each.  With the A operand in tensor memory an MMA reads
+    // only W's 2-4 KB from shared memory instead of 6-8 KB (the tensor pipe was pacing itself on those reads:
+    // profiles/r02_u_xs_trace_report.txt), the in-place hi store and the low-part ring (32 KB) are gone, and the
+    // X ring is two chunks deeper.  Reading one's own 128-byte row is conflict-free because of the swizzle
+    // (the 8 lanes of a quarter-warp hit 8 different 16-byte columns).
     {
-      const int ct = tid - 128;                      // 0 .. NCV*32-1
+      const int q = warp & 3;                        // TMEM lanes 32q .. 32q+31 belong to this warp
+      const int half = (warp - 4) >> 2;              // k-values 16*half .. 16*half+15 of the chunk
+      const int row = q * 32 + lane;
       uint32_t it = 0;
+      int sa = 0, sn = 0;
+      uint32_t ph_a = 0, ph_n = 0;
       for (int64_t t = u0; t < uend; t += ustep) {
         for (int kc = 0; kc < p.nkc; ++kc, ++it) {
-          const int sa = it % RA, sl = it % LO;
-          mbar_wait(FULLA(sa), (it / RA) & 1);
-          if (ct == 0) stamp(1, it);
-          mbar_wait(LOEMPTY(sl), ((it / LO) & 1) ^ 1);
-          if (ct == 0) stamp(2, it);
-          uint8_t* raw = ring + sa * CHUNK_A;
-          uint8_t* lop = lo + sl * CHUNK_A;
-          if (!(p.dbg & 2))
+          mbar_wait(FULLA(sa), ph_a);
+          mbar_wait(AEMPTY(sn), ph_n ^ 1);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          if (!(p.dbg & 2)) {
+            const uint8_t* src = ring + sa * CHUNK_A + row * 128;
+            uint32_t hi[16], lo[16];
 #pragma unroll
-          for (int j = 0; j < CHUNK_A / 16 / (NCV * 32); ++j) {
-            const int off = (ct + j * NCV * 32) * 16;
-            const uint4 v = *reinterpret_cast<const uint4*>(raw + off);
-            if constexpr (MODE == 0) {
-              uint4 o;
-              o.x = to_tf32(__uint_as_float(v.x) - __uint_as_float(v.x & 0xffffe000u));
-              o.y = to_tf32(__uint_as_float(v.y) - __uint_as_float(v.y & 0xffffe000u));
-              o.z = to_tf32(__uint_as_float(v.z) - __uint_as_float(v.z & 0xffffe000u));
-              o.w = to_tf32(__uint_as_float(v.w) - __uint_as_float(v.w & 0xffffe000u));
-              *reinterpret_cast<uint4*>(lop + off) = o;
+            for (int c = 0; c < 4; ++c) {
+              const uint4 v = *reinterpret_cast<const uint4*>(src + (((half * 4 + c) ^ (row & 7)) << 4));
+              const uint32_t x[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                hi[4 * c + e] = x[e] & 0xffffe000u;
+                if constexpr (MODE == 0) lo[4 * c + e] = to_tf32(__uint_as_float(x[e]) - __uint_as_float(x[e] & 0xffffe000u));
+              }
             }
-            *reinterpret_cast<uint4*>(raw + off) =
-                make_uint4(v.x & 0xffffe000u, v.y & 0xffffe000u, v.z & 0xffffe000u, v.w & 0xffffe000u);
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + 2 * BN + sn * A_COLS + half * 16;
+            tmem_st16(taddr, hi);
+            if constexpr (MODE == 0) tmem_st16(taddr + KC, lo);
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
           }
-          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic stores -> tensor core's proxy
-          mbar_arrive(CONV(sl));
-          if (ct == 0) stamp(3, it);
+          asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+          mbar_arrive(CONV(sn));
+          mbar_arrive(EMPTYA(sa));                     // this thread's reads of the raw chunk are done
+          if (warp == 3 + NCV && lane == 31) stamp(3, it);
+          if (++sa == RA) { sa = 0; ph_a ^= 1; }
+          if (++sn == NA) { sn = 0; ph_n ^= 1; }
         }
       }
     }
@@ -597,20 +630,24 @@ int xw_stream_run(const float* X, int64_t ldx, const float* W, int64_t ldw, int 
   // allows it, else streamed W chunks
   int bn = N <= 64 ? 64 : 128;
   bool wres = false;
+  // GCNB_XS_WRES_KB: most shared memory (KB) the resident W image of a 128-column tile may take; beyond it the tile
+  // is 64 columns wide (half the image, the X chunks read twice as often)
+  static const int wres_kb = getenv("GCNB_XS_WRES_KB") ? atoi(getenv("GCNB_XS_WRES_KB")) : 128;
   if (wres_ok) {
-    if (N > 64 && nkc * xs::w_chunk(128) <= 65536) { bn = 128; wres = true; }
+    if (N > 64 && nkc * xs::w_chunk(128) <= wres_kb * 1024) { bn = 128; wres = true; }
     else if (nkc * xs::w_chunk(64) <= 65536) { bn = 64; wres = true; }
   }
   int ntiles = (N + bn - 1) / bn;
   if (wres && ntiles > n_sm) { wres = false; bn = N <= 64 ? 64 : 128; ntiles = (N + bn - 1) / bn; }
   const int w_slots = wres ? nkc : 2;
-  // ring depths: GCNB_XS_LO low-part chunks (2..4, default 2), the rest of shared memory is the X ring (GCNB_XS_RA caps it)
-  static const int lo_env = getenv("GCNB_XS_LO") ? atoi(getenv("GCNB_XS_LO")) : 2;
+  // ring depths: GCNB_XS_NA converted chunks in tensor memory (2..4, default 4), all of shared memory that is left
+  // is the X ring (GCNB_XS_RA caps it)
+  static const int na_env = getenv("GCNB_XS_NA") ? atoi(getenv("GCNB_XS_NA")) : xs::NA_MAX;
   static const int ra_env = getenv("GCNB_XS_RA") ? atoi(getenv("GCNB_XS_RA")) : xs::RA_MAX;
-  const int lo_slots = std::max(2, std::min(xs::LO_MAX, lo_env));
-  const int ra = std::min(std::max(2, ra_env), xs::ring_a(bn, w_slots, lo_slots));
+  const int na_slots = std::max(2, std::min(xs::NA_MAX, na_env));
+  const int ra = std::min(std::max(2, ra_env), xs::ring_a(bn, w_slots));
   if (ra < 2) return 1;
-  const int smem = xs::fixed_bytes(bn, w_slots, lo_slots) + ra * xs::CHUNK_A;
+  const int smem = xs::fixed_bytes(bn, w_slots) + ra * xs::CHUNK_A;
   EncodeTiledFn enc = encode_tiled();
   if (!enc) return 1;
   CUtensorMap tmap;
@@ -632,7 +669,7 @@ int xw_stream_run(const float* X, int64_t ldx, const float* W, int64_t ldw, int 
   xs::Params p;
   p.w_img = img; p.D = D; p.ldd = ldd; p.mask_in = mask_in; p.mask_out = mask_out; p.ldm = ldm; p.bias = bias;
   p.M = M; p.N = N; p.K = K; p.nkc = nkc; p.ntiles = ntiles; p.mtiles = (M + xs::BM - 1) / xs::BM;
-  p.ra = ra; p.lo = lo_slots;
+  p.ra = ra; p.na = na_slots;
   p.epi = epi;
   p.keep_thresh = xs::drop_thresh(drop_p);
   p.scale = (epi & (GCNB_EPI_DROPOUT | GCNB_EPI_MASK)) ? 256.f / (256.f - (float)p.keep_thresh) : 1.f;
@@ -665,8 +702,8 @@ int xw_stream_run(const float* X, int64_t ldx, const float* W, int64_t ldw, int 
     if (cudaDeviceSynchronize() == cudaSuccess &&
         cudaMemcpy(host, p.trace, sizeof(host), cudaMemcpyDeviceToHost) == cudaSuccess) {
       if (FILE* f = fopen(trace_path, "a")) {
-        fprintf(f, "# M=%lld N=%d K=%d bn=%d wres=%d nkc=%d ra=%d lo=%d dbg=%d precision=%d\n", (long long)M, N, K, bn, (int)wres, nkc, ra,
-                lo_slots, p.dbg, precision);
+        fprintf(f, "# M=%lld N=%d K=%d bn=%d wres=%d nkc=%d ra=%d na=%d dbg=%d precision=%d\n", (long long)M, N, K, bn, (int)wres, nkc, ra,
+                na_slots, p.dbg, precision);
         for (int r = 0; r < 8; ++r) {
           fprintf(f, "%d", r);
           for (int i = 0; i < xs::kTraceLen; ++i) fprintf(f, " %llu", host[r * xs::kTraceLen + i]);

@@ -9,8 +9,9 @@
 // Blackwell's tensor core takes MN-major operands for tf32 (layout SWIZZLE_128B_BASE32B: rows = k, 128-byte rows
 // of 32 consecutive m), so no transposition is needed, only a re-layout of whole 16-byte chunks.
 // The first version of this kernel let TMA tensor-map boxes (16 vertices x 32 columns, SWIZZLE_128B_ATOM_32B)
-// write that layout directly; boxes made of 128-byte rows move at ~12+ cycles per row per SM (~2.5 TB/s over the
-// chip, DESIGN.md "Round 2"), so the products ran at a third of the HBM rate.  This version loads whole rows:
+// write that layout directly; this version loads whole rows with 1-D bulk copies (fewer, larger requests; both
+// stream at the HBM rate when >= 64 KB are in flight, profiles/r02_s_tma_stream_probe.jsonl — what made the first
+// version slow was its 2 516 partial matrices, DESIGN.md "Round 2: the dense products"):
 //   warp 0      producer: per stage of 16 vertices ONE 1-D bulk copy per operand (16 x M x 4 contiguous bytes when
 //               the matrix is dense in memory, else one per row) into a ring of raw stages
 //   warps 4-11  converters: raw rows -> hi = trunc13(x) and lo = tf32(x - hi) tiles of BOTH operands, written
@@ -185,13 +186,13 @@ xt_kernel(const Params p) {
 
   if (warp == 0) {
     // ---------------- producer: 1-D bulk copies of whole rows (one per operand and stage when the rows are
-    // contiguous, else one per row) — the TMA unit moves large contiguous ranges at full rate, while tensor-map
-    // boxes of 128-byte rows (the first version of this kernel) are limited to ~12 cycles per row per SM ----------------
+    // contiguous, else one per row: small copies cost ~300 cycles each, tools/tma_stream_probe.cu) ----------------
     if (lane == 0) {
       const bool a_contig = p.lda == p.M, b_contig = p.ldb == p.N;
-      for (int it = 0; it < nst; ++it) {
-        const int s = it % RAWS;
-        mbar_wait(EMPTY(s), ((it / RAWS) & 1) ^ 1);
+      int s = 0;               // ring position / phase as counters (no integer division per stage)
+      uint32_t ph = 0;
+      for (int it = 0; it < nst; ++it, s = (s + 1 == RAWS ? 0 : s + 1), ph ^= (s == 0)) {
+        mbar_wait(EMPTY(s), ph ^ 1);
         const int64_t v = v0 + (int64_t)it * KV;
         const int rows = (int)(v1 - v < KV ? v1 - v : KV);
         const uint32_t full = FULL(s);
@@ -221,8 +222,8 @@ xt_kernel(const Params p) {
     // loop of ~17 instructions (xw_stream.cu) ----------------
     {
       const uint32_t idesc = make_idesc(n_umma);
+      int grp = 0, pos = 0;
       for (int it = 0; it < nst; ++it) {
-        const int grp = it / p.chain, pos = it - grp * p.chain;
         const uint32_t buf = grp & 1;
         if (pos == 0) mbar_wait(TEMPTY(buf), ((grp >> 1) & 1) ^ 1);
         const uint32_t tmem_d = tmem_base + buf * 256;
@@ -247,6 +248,7 @@ xt_kernel(const Params p) {
           if (pos == p.chain - 1 || it == nst - 1) commit(TFULL(buf));
         }
         __syncwarp();
+        if (++pos == p.chain) { pos = 0; ++grp; }
       }
     }
   } else if (warp >= 4 && warp < 4 + NC) {
@@ -254,9 +256,11 @@ xt_kernel(const Params p) {
     const int ct = tid - 128;                        // 0 .. NC*32-1
     const int mpc = p.M >> 2, npc = p.N >> 2;        // 16-byte chunks per row
     const uint32_t inv_m = (65536u + (uint32_t)mpc - 1) / (uint32_t)mpc, inv_n = (65536u + (uint32_t)npc - 1) / (uint32_t)npc;
+    int s = 0;
+    uint32_t ph = 0;
     for (int it = 0; it < nst; ++it) {
-      const int s = it % RAWS, cs = it % CS;
-      mbar_wait(FULL(s), (it / RAWS) & 1);
+      const int cs = it % CS;
+      mbar_wait(FULL(s), ph);
       mbar_wait(CEMPTY(cs), ((it / CS) & 1) ^ 1);
       const int64_t v = v0 + (int64_t)it * KV;
       const int rows = (int)(v1 - v < KV ? v1 - v : KV);
@@ -292,6 +296,7 @@ xt_kernel(const Params p) {
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic stores -> tensor core's proxy
       mbar_arrive(CONV(cs));
       mbar_arrive(EMPTY(s));                          // this thread's reads of the raw stage are done
+      if (++s == RAWS) { s = 0; ph ^= 1; }
     }
   } else if (warp >= 4 + NC) {
     // ---------------- epilogue: accumulator -> partial matrix ----------------
