@@ -348,28 +348,41 @@ xt_kernel(const Params p) {
 }
 
 // D (+bias)(ReLU) = sum of the CTAs' partial matrices in a fixed order; `transposed`: the partials are [N x M] = D^T.
-// Row M of the partials (ones column, direct route only) goes to colsum[0..N).
-__global__ void __launch_bounds__(256)
-xt_reduce_kernel(const float* __restrict__ part, int n_cta, int64_t K, int64_t v_per_cta, int M1, int Mp, int Np,
-                 int transposed, float* __restrict__ D, int64_t ldd, int M, int N, const float* __restrict__ bias,
-                 int epi, int ones_row, float* __restrict__ colsum) {
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;     // element of the partial matrix (M1 x Np)
-  if (idx >= M1 * Np) return;
-  float s = 0.f;
-  for (int c = 0; c < n_cta; ++c) {
-    if ((int64_t)c * v_per_cta >= K) break;                   // trailing CTAs without vertices wrote nothing
-    s += part[(int64_t)c * M1 * Np + idx];
+// Row M of the partials (ones column, direct route only) goes to colsum[0..N).  One thread per 4 consecutive
+// elements of a row (Np is a multiple of 4), 8 independent loads in flight.
+__global__ void __launch_bounds__(128)
+xt_reduce_kernel(const float* __restrict__ part, int n_valid, int M1, int Mp, int Np, int transposed,
+                 float* __restrict__ D, int64_t ldd, int M, int N, const float* __restrict__ bias, int epi, int ones_row,
+                 float* __restrict__ colsum) {
+  const int idx4 = blockIdx.x * blockDim.x + threadIdx.x;    // group of 4 elements of the partial matrix (M1 x Np)
+  const int total = M1 * Np;
+  if (idx4 * 4 >= total) return;
+  const float4* src = reinterpret_cast<const float4*>(part) + idx4;
+  const int64_t stride4 = (int64_t)total / 4;
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 8
+  for (int c = 0; c < n_valid; ++c) {
+    const float4 v = __ldcs(src + (int64_t)c * stride4);
+    s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
   }
-  const int pr = idx / Np, pc = idx % Np;
+  const int pr = (idx4 * 4) / Np, pc = (idx4 * 4) % Np;
+  const float o[4] = {s.x, s.y, s.z, s.w};
   if (pr >= Mp) {
-    if (pr == ones_row && colsum) colsum[pc] = s;
+    if (pr == ones_row && colsum) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) colsum[pc + e] = o[e];
+    }
     return;
   }
-  const int r = transposed ? pc : pr, c = transposed ? pr : pc;
-  if (r >= M || c >= N) return;
-  if (epi & GCNB_EPI_BIAS) s += __ldg(bias + c);
-  if (epi & GCNB_EPI_RELU) s = fmaxf(s, 0.f);
-  D[(int64_t)r * ldd + c] = s;
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const int r = transposed ? pc + e : pr, c = transposed ? pr : pc + e;
+    if (r >= M || c >= N) continue;
+    float v = o[e];
+    if (epi & GCNB_EPI_BIAS) v += __ldg(bias + c);
+    if (epi & GCNB_EPI_RELU) v = fmaxf(v, 0.f);
+    D[(int64_t)r * ldd + c] = v;
+  }
 }
 
 }  // namespace xt
@@ -427,8 +440,10 @@ int xw_tallk_stream_run(const float* X, int64_t ldx, const float* W, int64_t ldw
   int rc = GCNB_OK;
   if (cudaGetLastError() != cudaSuccess) rc = set_error(GCNB_ERR_CUDA, "xt_kernel launch failed");
   if (rc == GCNB_OK) {
-    xt::xt_reduce_kernel<<<(unsigned)((p.M1 * Np + 255) / 256), 256, 0, stream>>>(
-        part, grid, K, p.v_per_cta, p.M1, Mp, Np, direct ? 0 : 1, D, ldd, (int)M, N, bias, epi, p.ones_col, colsum);
+    // CTAs past the end of K wrote nothing
+    const int n_valid = (int)std::min<int64_t>(grid, (K + p.v_per_cta - 1) / p.v_per_cta);
+    xt::xt_reduce_kernel<<<(unsigned)((p.M1 * Np / 4 + 127) / 128), 128, 0, stream>>>(
+        part, n_valid, p.M1, Mp, Np, direct ? 0 : 1, D, ldd, (int)M, N, bias, epi, p.ones_col, colsum);
     if (cudaGetLastError() != cudaSuccess) rc = set_error(GCNB_ERR_CUDA, "xt_reduce_kernel launch failed");
   }
   cudaFreeAsync(part, stream);

@@ -520,18 +520,26 @@ int xw_tallk_stream_run(const float* X, int64_t ldx, const float* W, int64_t ldw
                         int N, int64_t K, const float* bias, int epi, int precision, int n_sm, float* colsum,
                         cudaStream_t stream);                                                              // xw_tallk_stream.cu
 // column sums of a row-major [K x N] matrix in two fixed-order passes (the fall-back of gcnb_xw_tn_colsum when
-// the product kernel has no spare row for the ones column): slabs of kColsumRows rows -> part[slab][N] -> out[N]
-constexpr int kColsumRows = 4096;
+// the product kernel has no spare row for the ones column): slabs of kColsumRows rows -> part[slab][N] -> out[N].
+// Every thread owns 4 columns of one row out of 8 at a time, four rows in flight; the second pass sums a column's
+// slab values with 256 threads in a fixed order (strided partial sums, then a shared-memory tree).
+constexpr int kColsumRows = 512;
 __global__ void __launch_bounds__(256)
 colsum_slab_kernel(const float* __restrict__ G, int64_t ldg, int64_t K, int N, float* __restrict__ part) {
   __shared__ float sh[8][33];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int64_t r0 = (int64_t)blockIdx.x * kColsumRows, r1 = r0 + kColsumRows < K ? r0 + kColsumRows : K;
   for (int c0 = 0; c0 < N; c0 += 32) {
-    float s = 0.f;
-    if (c0 + tx < N)
-      for (int64_t r = r0 + ty; r < r1; r += 8) s += G[r * ldg + c0 + tx];
-    sh[ty][tx] = s;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    if (c0 + tx < N) {
+      const float* g = G + c0 + tx;
+      int64_t r = r0 + ty;
+      for (; r + 24 < r1; r += 32) {
+        s0 += g[r * ldg]; s1 += g[(r + 8) * ldg]; s2 += g[(r + 16) * ldg]; s3 += g[(r + 24) * ldg];
+      }
+      for (; r < r1; r += 8) s0 += g[r * ldg];
+    }
+    sh[ty][tx] = (s0 + s1) + (s2 + s3);
     __syncthreads();
     if (ty == 0 && c0 + tx < N) {
       float t = 0.f;
@@ -544,11 +552,17 @@ colsum_slab_kernel(const float* __restrict__ G, int64_t ldg, int64_t K, int N, f
 }
 __global__ void __launch_bounds__(256)
 colsum_final_kernel(const float* __restrict__ part, int slabs, int N, float* __restrict__ out) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= N) return;
+  __shared__ float sh[256];
+  const int c = blockIdx.x;                      // one block per column
   float s = 0.f;
-  for (int b = 0; b < slabs; ++b) s += part[(int64_t)b * N + c];
-  out[c] = s;
+  for (int b = threadIdx.x; b < slabs; b += 256) s += part[(int64_t)b * N + c];
+  sh[threadIdx.x] = s;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) out[c] = sh[0];
 }
 // elementwise tail of gcnb_xw_ex for the products that do not run on the streaming kernel: one thread per
 // (row, 32-column word of the bit masks); same dropout hash (one word per 4 columns, one byte per element)
@@ -765,7 +779,7 @@ extern "C" int gcnb_xw_tn_colsum(const float* X, int64_t ldx, const float* G, in
   colsum_slab_kernel<<<slabs, 256, 0, stream>>>(G, ldg, K, N, part);
   rc = cudaGetLastError() == cudaSuccess ? GCNB_OK : set_error(GCNB_ERR_CUDA, "colsum_slab_kernel launch failed");
   if (rc == GCNB_OK) {
-    colsum_final_kernel<<<(N + 255) / 256, 256, 0, stream>>>(part, slabs, N, colsum);
+    colsum_final_kernel<<<N, 256, 0, stream>>>(part, slabs, N, colsum);
     if (cudaGetLastError() != cudaSuccess) rc = set_error(GCNB_ERR_CUDA, "colsum_final_kernel launch failed");
   }
   cudaFreeAsync(part, stream);
