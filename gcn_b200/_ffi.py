@@ -60,6 +60,8 @@ SIGNATURES = {
     "gcnb_xw_tn_colsum": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int, c_int,
                                   c_int, c_void_p]),
     "gcnb_dropout_keeps": (c_int, [c_int64, c_int, c_int, ctypes.c_float, ctypes.c_uint32]),
+    "gcnb_colsum_noalloc": (c_int, [c_void_p, c_int64, c_int64, c_int, c_void_p, c_void_p]),
+    "gcnb_colsum_noalloc_max_floats": (c_int64, []),
     "gcnb_logsoftmax_nll_fwd": (c_int, [c_void_p, c_int64, c_int64, c_int, c_void_p, c_void_p, c_int64, c_int64,
                                         c_void_p, c_int64, c_void_p, c_void_p]),
     "gcnb_logsoftmax_nll_bwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int,

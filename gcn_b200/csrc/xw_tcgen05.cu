@@ -785,3 +785,66 @@ extern "C" int gcnb_xw_tn_colsum(const float* X, int64_t ldx, const float* G, in
   cudaFreeAsync(part, stream);
   return rc;
 }
+
+// ---- column sums without any allocation (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA-graph capture, tight serving loops) -------------------
+// The slab partials of colsum_slab_kernel live in a file-scope device array instead of a pool allocation.  Every
+// device that loads the library holds these 8 MiB until exit.  The array name below is a HOST-side stand-in in host
+// code: its device address is looked up once per device with cudaGetSymbolAddress and that pointer is what the
+// kernels receive.  All calls share the array: two calls that overlap on one GPU (different streams) race.
+// Nothing needs clearing: the first pass writes every part[slab][0..N) the second pass reads.
+namespace {
+constexpr int64_t kNoAllocScratchFloats = (int64_t)2 << 20;              // 8 MiB
+constexpr int kNoAllocMaxDevices = 64;
+static __device__ __align__(256) float g_colsum_scratch[kNoAllocScratchFloats];
+std::atomic<float*> g_colsum_scratch_addr[kNoAllocMaxDevices];
+
+// device address of the scratch array on `dev` (which the caller has made current); nullptr + error on failure
+int colsum_scratch_for(int dev, float** out) {
+  GCNB_REQUIRE(dev >= 0 && dev < kNoAllocMaxDevices, "device %d beyond the %d devices the no-alloc table holds", dev,
+               kNoAllocMaxDevices);
+  float* p = g_colsum_scratch_addr[dev].load(std::memory_order_acquire);
+  if (p == nullptr) {
+    void* sym = nullptr;
+    GCNB_CHECK_CUDA(cudaGetSymbolAddress(&sym, g_colsum_scratch));
+    GCNB_REQUIRE(sym != nullptr, "cudaGetSymbolAddress returned a null scratch address on device %d", dev);
+    p = static_cast<float*>(sym);
+    g_colsum_scratch_addr[dev].store(p, std::memory_order_release);
+  }
+  *out = p;
+  return GCNB_OK;
+}
+}  // namespace
+
+extern "C" int64_t gcnb_colsum_noalloc_max_floats(void) { return kNoAllocScratchFloats; }
+
+extern "C" int gcnb_colsum_noalloc(const float* G, int64_t ldg, int64_t K, int N, float* colsum, void* stream_) {
+  GCNB_REQUIRE(K >= 0 && N >= 0, "negative size (K=%lld N=%d)", (long long)K, N);
+  GCNB_REQUIRE(N == 0 || colsum != nullptr, "colsum is null");
+  if (N == 0) return GCNB_OK;
+  const int64_t slabs = (K + kColsumRows - 1) / kColsumRows;
+  GCNB_REQUIRE(slabs * (int64_t)N <= kNoAllocScratchFloats,
+               "gcnb_colsum_noalloc: ceil(K/%d)*N = %lld partial sums exceed the %lld-float static scratch "
+               "(K=%lld N=%d); use gcnb_xw_tn_colsum",
+               kColsumRows, (long long)(slabs * (int64_t)N), (long long)kNoAllocScratchFloats, (long long)K, N);
+  int rc = require_gpu();
+  if (rc != GCNB_OK) return rc;
+  const int dev = pointer_device(colsum);
+  GCNB_REQUIRE(dev >= 0, "colsum is not a device pointer");
+  DeviceGuard guard(dev);
+  GCNB_CHECK_CUDA(guard.status);
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (K == 0) {
+    GCNB_CHECK_CUDA(cudaMemsetAsync(colsum, 0, (size_t)N * sizeof(float), stream));
+    return GCNB_OK;
+  }
+  GCNB_REQUIRE(G != nullptr && ldg >= N, "G is null or ldg < N");
+  float* part = nullptr;
+  rc = colsum_scratch_for(dev, &part);
+  if (rc != GCNB_OK) return rc;
+  colsum_slab_kernel<<<(unsigned)slabs, 256, 0, stream>>>(G, ldg, K, N, part);
+  if (cudaGetLastError() != cudaSuccess) return set_error(GCNB_ERR_CUDA, "colsum_slab_kernel launch failed");
+  colsum_final_kernel<<<N, 256, 0, stream>>>(part, (int)slabs, N, colsum);
+  if (cudaGetLastError() != cudaSuccess) return set_error(GCNB_ERR_CUDA, "colsum_final_kernel launch failed");
+  return GCNB_OK;
+}

@@ -136,6 +136,16 @@ int gcnb_xw_ex(const float* X, int64_t ldx, int trans_x, const float* W, int64_t
 int gcnb_xw_tn_colsum(const float* X, int64_t ldx, const float* G, int64_t ldg, float* D, int64_t ldd,
                       float* colsum, int64_t M, int N, int K, int precision, void* stream);
 int gcnb_dropout_keeps(int64_t row, int col, int N, float drop_p, uint32_t seed);
+/* colsum[N] = 1^T·G for a row-major G [K x N], like the column-sum half of gcnb_xw_tn_colsum, but ALLOCATING NOTHING:
+ * no cudaMalloc / cudaMallocAsync / cudaFree, no library workspace.  It has no counterpart in the reference; it was
+ * added for callers that cannot allocate (code under CUDA-graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc).  The per-slab partial sums go to a static device array of
+ * gcnb_colsum_noalloc_max_floats() = 2 Mi floats (8 MiB, held by every GPU that loads the library until exit):
+ * ceil(K/512)·N must not exceed it, else GCNB_ERR_ARG with the sizes in gcnb_last_error().  Every call shares the
+ * array, so calls that overlap on one GPU (different streams, or one stream per thread) race; calls on one stream
+ * are ordered.  Deterministic (fixed summation order), same result as gcnb_xw_tn_colsum's two-pass column sums. */
+int gcnb_colsum_noalloc(const float* G, int64_t ldg, int64_t K, int N, float* colsum, void* stream);
+int64_t gcnb_colsum_noalloc_max_floats(void);
 
 /* Fused log-softmax + NLL of the GCN head (replaces F.log_softmax, pygcn/gcn6.py:248, and
  * F.nll_loss(output[idx_train], labels[idx_train]), gcn6.py:427) and its gradient.  DEVICE pointers.

@@ -17,7 +17,7 @@ HEADER = os.path.join(ROOT, "include", "gcn_b200.h")
 def declared_symbols():
     text = open(HEADER).read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    return sorted(set(re.findall(r"^\s*(?:const\s+)?(?:int|void|char\s*\*|const char\s*\*)\s+\*?(\w+)\s*\(",
+    return sorted(set(re.findall(r"^\s*(?:const\s+)?(?:int|int64_t|void|char\s*\*|const char\s*\*)\s+\*?(\w+)\s*\(",
                                  text, flags=re.M)))
 
 
