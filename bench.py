@@ -797,9 +797,9 @@ def run_epoch_multi(args):
         raise SystemExit(f"bench.py: parity_check failed: {parity['max_rel_err']:.3e} > {parity['tol']}")
 
 
-def partition_parity_check(part, rp, ci, va, k, device, tol, steps=4, rows=256):
+def partition_parity_check(part, rp, ci, va, k, device, tol, steps=6, rows=256):
     """Untimed self-check of the N-GPU path: `steps` consecutive partitioned SpMMs
-    under the REAL stream-ordered rank barrier (gcn_b200.dist._rank_barrier, an NCCL all-reduce), each with
+    under the REAL stream-ordered rank barrier (gcn_b200.dist._rank_barrier), each with
     a fresh operand (so that a stale exchange slot cannot pass; both slots are reused from step 3 on), and
     `rows` sampled rows of this rank's result compared with an fp64 host evaluation of the same rows of
     Â·B.  Returns {"max_rel_err", "rows", "steps", "tol", "ok"}, the error being the max over ranks of
@@ -810,21 +810,32 @@ def partition_parity_check(part, rp, ci, va, k, device, tol, steps=4, rows=256):
     rng = np.random.default_rng(1234 + rank)
     worst = 0.0
     n_rows = 0
+    # operands and, for the reference only, every rank's operand (a plain NCCL all-gather of the padded blocks),
+    # all prepared BEFORE the steps, so that the steps themselves run back to back without a host synchronisation
+    # between them: a rank may be a whole step ahead of a peer, which is when a stale or overwritten slot would show
+    Bs, fulls = [], []
     for s in range(steps):
         g = torch.Generator(device=device).manual_seed(1000 * (s + 1) + rank)
         B = torch.randn(part.m_local, k, device=device, generator=g)
-        slot = part.next_operand(k)
-        if slot is not None:        # fp32 pull mode: the producer writes into the free exchange slot
-            slot.copy_(B)
-            op = slot
-        else:
-            op = B
-        out = part.forward(op)
-        # every rank's operand, for the reference only: a plain NCCL all-gather of the padded blocks
         padded = torch.zeros(stride, k, device=device)
         padded[: part.m_local] = B
         full = torch.empty(world * stride, k, device=device)
         dist.all_gather_into_tensor(full, padded, group=part.group)
+        Bs.append(B)
+        fulls.append(full)
+    torch.cuda.synchronize(device)
+    outs = []
+    for s in range(steps):
+        slot = part.next_operand(k)
+        if slot is not None:        # fp32 pull mode: the producer writes into the free exchange slot
+            slot.copy_(Bs[s])
+            op = slot
+        else:
+            op = Bs[s]
+        outs.append(part.forward(op))
+    torch.cuda.synchronize(device)
+    for s in range(steps):
+        out, full = outs[s], fulls[s]
         pick = np.sort(rng.choice(part.m_local, size=min(rows, part.m_local), replace=False))
         got = out[torch.from_numpy(pick).to(device)].double().cpu().numpy()
         ref = np.zeros((len(pick), k))
@@ -843,7 +854,10 @@ def partition_parity_check(part, rp, ci, va, k, device, tol, steps=4, rows=256):
     dist.all_reduce(cnt, op=dist.ReduceOp.SUM, group=part.group)
     err = float(t.item())
     return {"max_rel_err": err, "rows": int(cnt.item()), "steps": steps, "tol": tol, "ok": bool(err <= tol),
-            "barrier": "gcn_b200.dist._rank_barrier (stream-ordered NCCL all-reduce), fresh operand every step",
+            "barrier": "gcn_b200.dist._rank_barrier (" + ("flags in peer memory, gcnb_peer_barrier"
+                                                        if getattr(part, "_peer_flags", None) is not None
+                                                        else "stream-ordered NCCL all-reduce")
+                       + "), fresh operand every step, steps back to back without a host synchronisation",
             "reference": "fp64 host evaluation of the sampled rows of A·B"}
 
 

@@ -70,6 +70,7 @@ SIGNATURES = {
     "gcnb_peer_free": (c_int, [c_int, c_void_p]),
     "gcnb_peer_open": (c_int, [c_int, c_void_p, POINTER(c_void_p)]),
     "gcnb_peer_close": (c_int, [c_int, c_void_p]),
+    "gcnb_peer_barrier": (c_int, [c_void_p, c_int, c_int, ctypes.c_uint32, c_void_p]),
     "gcnb_pull_rows": (c_int, [c_void_p, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_int64,
                                c_int64, c_int64, c_int64, c_void_p]),
     "gcnb_order_deg": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, c_void_p]),

@@ -198,6 +198,13 @@ static int upload_matrix(const int32_t* rowptr, const int32_t* col, const float*
   int64_t s_n_partials = 0;
   {
     const int64_t seg_nnz = seg_target(nnz, n_sm);
+    // On a small matrix (seg_nnz below kSegNnz: the remote-column block of a row partition, 1.4 M non-zeros
+    // at 8 GPUs) a 1024-non-zero piece of a hub row is a serial chain of 256 ring turns, each an HBM latency:
+    // it alone took 0.25 ms while the other warps were done after 0.08 (profiles/r02_af_*).  Rows are
+    // therefore "long" from 2 x seg_nnz non-zeros on and cut into pieces of at most that.
+    static const int short_pieces = getenv("GCNB_SHORT_PIECES") ? atoi(getenv("GCNB_SHORT_PIECES")) : 1;
+    const int64_t long_row = short_pieces ? std::min<int64_t>(kLongRow, std::max<int64_t>(128, 2 * seg_nnz)) : kLongRow;
+    const int64_t seg_long = short_pieces ? std::min<int64_t>(kSegLong, std::max<int64_t>(128, 2 * seg_nnz)) : kSegLong;
     int64_t r0 = -1;
     auto close_run = [&](int64_t r_end) {
       if (r0 >= 0) segs.push_back({(int32_t)r0, (int32_t)r_end, rowptr[r0], rowptr[r_end]});
@@ -205,12 +212,12 @@ static int upload_matrix(const int32_t* rowptr, const int32_t* col, const float*
     };
     for (int64_t r = 0; r < m; ++r) {
       const int64_t beg = rowptr[r], end = rowptr[r + 1], len = end - beg;
-      if (len >= kLongRow) {
+      if (len >= long_row) {
         close_run(r);
-        if (len <= kSegLong) {
+        if (len <= seg_long) {
           segs.push_back({(int32_t)r, (int32_t)(r + 1), (int32_t)beg, (int32_t)end});
         } else {
-          const int64_t pieces = (len + kSegLong - 1) / kSegLong;
+          const int64_t pieces = (len + seg_long - 1) / seg_long;
           const int64_t per = (len + pieces - 1) / pieces;
           s_split_rows.push_back((int32_t)r);
           s_split_ptr.push_back((int32_t)s_n_partials);
@@ -490,9 +497,29 @@ static int launch_packed(const LaunchArgs& a) {
   const int64_t gs = (M.n_segs + kStreamWarps - 1) / kStreamWarps;
   if (gs > 0x7fffffffLL || a.ldb * (int64_t)sizeof(TB) > 0xffffffffLL)
     return set_error(GCNB_ERR_UNSUPPORTED, "matrix too large for one grid");
-  spmm_stream_packed_kernel<TB, VEC, S, U, MINB><<<(unsigned)gs, kStreamWarps * 32, 0, a.stream>>>(
-      M.segs, (int)M.n_segs, M.rowptr, M.cv, (const TB*)a.B, (uint32_t)(a.ldb * sizeof(TB)), a.C, a.ldc,
-      a.partials, a.k, a.bias, a.epi);
+  static const int l2pol = getenv("GCNB_L2POL") ? atoi(getenv("GCNB_L2POL")) : 1;
+  const int l2 = ((l2pol & 1) ? kL2Streams : 0) | ((l2pol & 2) ? kL2BLast : 0);
+  if constexpr (sizeof(TB) == 4 && VEC == 8) {
+    // 256-bit loads: a ring slot is 8 registers.  GCNB_PACKED_CFG picks ring depth / CTAs per SM (experiments)
+    static const int pcfg = getenv("GCNB_PACKED_CFG") ? atoi(getenv("GCNB_PACKED_CFG")) : 0;
+    auto go = [&](auto kern) {
+      kern<<<(unsigned)gs, kStreamWarps * 32, 0, a.stream>>>(
+          M.segs, (int)M.n_segs, M.rowptr, M.cv, (const TB*)a.B, (uint32_t)(a.ldb * sizeof(TB)), a.C, a.ldc,
+          a.partials, a.k, a.bias, a.epi | l2);
+    };
+    // registers (ptxas, S = 2): U=2 at 6 CTAs/SM 78, U=4 at 4 CTAs/SM 118, U=8 at 3 CTAs/SM 162, none spilling;
+    // U=2 at 8 CTAs/SM (64 registers) spills a ring slot
+    constexpr int U8 = 8 * S <= 32 ? 8 : 32 / S;   // a ring turn must fit a 32-entry slab
+    if (pcfg == 1) go(spmm_stream_packed_kernel<TB, VEC, S, 4, 4>);
+    else if (pcfg == 2) go(spmm_stream_packed_kernel<TB, VEC, S, U8, 3>);
+    else if (pcfg == 3) go(spmm_stream_packed_kernel<TB, VEC, S, 2, 8>);
+    else if (pcfg == 4) go(spmm_stream_packed_kernel<TB, VEC, S, 4, 5>);
+    else go(spmm_stream_packed_kernel<TB, VEC, S, 2, 6>);
+  } else {
+    spmm_stream_packed_kernel<TB, VEC, S, U, MINB><<<(unsigned)gs, kStreamWarps * 32, 0, a.stream>>>(
+        M.segs, (int)M.n_segs, M.rowptr, M.cv, (const TB*)a.B, (uint32_t)(a.ldb * sizeof(TB)), a.C, a.ldc,
+        a.partials, a.k, a.bias, a.epi | l2);
+  }
   GCNB_CHECK_CUDA(cudaGetLastError());
   if (M.s_n_split > 0) {
     spmm_reduce_kernel<<<(unsigned)M.s_n_split, 128, 0, a.stream>>>(
@@ -570,6 +597,41 @@ static int launch_vec(const LaunchArgs& a) {
 
 static inline bool aligned(const void* p, size_t a) { return ((uintptr_t)p % a) == 0; }
 
+// fp32 feature rows through 256-bit loads (VEC = 8): half the warp-wide gather requests of the 128-bit kernels.
+// Needs 32-byte aligned rows (B and its pitch) whose pitch covers k rounded up to 8.  Only the stream classes:
+//   k <= 32 / 64 / 128 on matrices with >= 24 nnz/row: packed, 8 / 4 / 2 rows per request
+//   k <= 256: one request per row (NV = 1), wider: NV = 2 per column tile of 512
+// returns 1 when the shape is left to the 128-bit kernels
+static int launch_vec8(const LaunchArgs& a, int mask) {
+  const int nvec = (a.k + 7) / 8;
+  const Matrix& M = *a.M;
+  if (M.n_segs == 0) return 1;
+  if (M.p_n_items > 0 && !(a.epi & GCNB_EPI_ACCUM)) return 1;   // panel class chosen at plan time
+  static const int packed = getenv("GCNB_PACKED") ? atoi(getenv("GCNB_PACKED")) : 8;
+  if (nvec <= 16) {
+    if (!(mask & 1) || packed < 2 || M.nnz < 24 * M.m) return 1;
+    if (nvec <= 4 && packed >= 8) return launch_packed<float, 8, 8>(a);
+    if (nvec <= 8 && packed >= 4) return launch_packed<float, 8, 4>(a);
+    return launch_packed<float, 8, 2>(a);
+  }
+  if (!(mask & 2)) return 1;
+  if (a.ldb * 4 > 0xffffffffLL) return 1;
+  const int tiles = (nvec + 63) / 64;
+  const int nv = (nvec + 32 * tiles - 1) / (32 * tiles);
+  const int64_t gs = (M.n_segs + kStreamWarps - 1) / kStreamWarps;
+  if (gs > 0x7fffffffLL) return 1;
+  const unsigned ytiles = (unsigned)((a.k + 32 * nv * 8 - 1) / (32 * nv * 8));
+  int rc = nv <= 1 ? launch_stream<float, 8, 1>(a, gs, ytiles) : launch_stream<float, 8, 2>(a, gs, ytiles);
+  if (rc != GCNB_OK) return rc;
+  GCNB_CHECK_CUDA(cudaGetLastError());
+  if (M.s_n_split > 0) {
+    spmm_reduce_kernel<<<(unsigned)M.s_n_split, 128, 0, a.stream>>>(
+        M.s_split_rows, M.s_split_ptr, a.partials, a.C, a.ldc, a.k, a.bias, a.epi);
+    GCNB_CHECK_CUDA(cudaGetLastError());
+  }
+  return GCNB_OK;
+}
+
 static int spmm_dispatch(const Matrix& M, const void* B, int b_dtype, int64_t ldb, float* C,
                          int64_t ldc, int k, const float* bias, int epi, cudaStream_t stream) {
   if (M.m == 0 || k == 0) return GCNB_OK;
@@ -582,6 +644,16 @@ static int spmm_dispatch(const Matrix& M, const void* B, int b_dtype, int64_t ld
   // vector width: limited by k, both leading dimensions and base alignment (C is stored with
   // min(VEC,4) floats per store)
   static const int max_vec = getenv("GCNB_MAX_VEC") ? atoi(getenv("GCNB_MAX_VEC")) : 4;   // experiments
+  // GCNB_F32_V8: bit 0 = 256-bit packed kernels (k <= 128), bit 1 = 256-bit stream kernel (k > 128)
+  static const int f32_v8 = getenv("GCNB_F32_V8") ? atoi(getenv("GCNB_F32_V8")) : 0;
+  if (b_dtype == GCNB_F32 && f32_v8 && k % 4 == 0 && ldb % 8 == 0 && ldb >= (k + 7) / 8 * 8 && ldc % 4 == 0 &&
+      aligned(B, 32) && aligned(C, 16)) {
+    rc = launch_vec8(a, f32_v8);
+    if (rc != 1) {
+      if (partials) cudaFreeAsync(partials, stream);
+      return rc;
+    }
+  }
   if (b_dtype == GCNB_F32) {
     if (max_vec >= 4 && k % 4 == 0 && ldb % 4 == 0 && ldc % 4 == 0 && aligned(B, 16) && aligned(C, 16))
       rc = launch_vec<float, 4, 4>(a);

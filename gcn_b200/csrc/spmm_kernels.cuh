@@ -75,6 +75,18 @@ __device__ __forceinline__ void ldg_hint(const void* p, uint64_t pol, uint4& v) 
   asm volatile("ld.global.nc.L2::cache_hint.v4.b32 {%0, %1, %2, %3}, [%4], %5;"
                : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p), "l"(pol));
 }
+// 256-bit load (sm_100: LDG.E.ENL2.256): one lane brings 32 bytes, so a 400-byte feature row needs 13 lanes
+// and ONE warp-wide request can carry two rows.  The address must be 32-byte aligned.
+__device__ __forceinline__ void ldg_hint256(const void* p, uint64_t pol, float (&w)[8]) {
+  asm volatile("ld.global.nc.L2::cache_hint.v8.f32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8], %9;"
+               : "=f"(w[0]), "=f"(w[1]), "=f"(w[2]), "=f"(w[3]), "=f"(w[4]), "=f"(w[5]), "=f"(w[6]), "=f"(w[7])
+               : "l"(p), "l"(pol));
+}
+__device__ __forceinline__ void ldg256(const void* p, float (&w)[8]) {
+  asm volatile("ld.global.nc.v8.f32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=f"(w[0]), "=f"(w[1]), "=f"(w[2]), "=f"(w[3]), "=f"(w[4]), "=f"(w[5]), "=f"(w[6]), "=f"(w[7])
+               : "l"(p));
+}
 __device__ __forceinline__ void ldg_hint(const void* p, uint64_t pol, uint2& v) {
   asm volatile("ld.global.nc.L2::cache_hint.v2.b32 {%0, %1}, [%2], %3;" : "=r"(v.x), "=r"(v.y) : "l"(p), "l"(pol));
 }
@@ -98,6 +110,14 @@ struct VecLoad<float, 4> {
   static __device__ __forceinline__ void load_plain(const float* p, float (&o)[4]) {
     const float4 v = *reinterpret_cast<const float4*>(p);
     o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w;
+  }
+};
+template <>
+struct VecLoad<float, 8> {
+  static __device__ __forceinline__ void load(const float* p, float (&o)[8]) { ldg256(p, o); }
+  static __device__ __forceinline__ void load_plain(const float* p, float (&o)[8]) {
+    const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+    o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w; o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
   }
 };
 template <>
@@ -161,7 +181,9 @@ struct RawVec<float, VEC> {
   float w[VEC];
   __device__ __forceinline__ void load(const float* p) { VecLoad<float, VEC>::load(p, w); }
   __device__ __forceinline__ void load(const float* p, uint64_t pol) {
-    if constexpr (VEC == 4) {
+    if constexpr (VEC == 8) {
+      ldg_hint256(p, pol, w);
+    } else if constexpr (VEC == 4) {
       uint4 v; ldg_hint(p, pol, v);
       w[0] = __uint_as_float(v.x); w[1] = __uint_as_float(v.y); w[2] = __uint_as_float(v.z); w[3] = __uint_as_float(v.w);
     } else if constexpr (VEC == 2) {
@@ -263,6 +285,34 @@ __device__ __forceinline__ void load_c(const float* p, float (&v)[VEC]) {
     v[0] = q.x; v[1] = q.y;
   } else {
     v[0] = *p;
+  }
+}
+
+// number of the VEC columns starting at `coff` that exist (k is a multiple of 4 whenever VEC is 8: a lane of the
+// 256-bit kernels may own 4 real columns and 4 of the row's padding)
+template <int VEC>
+__device__ __forceinline__ int cols_valid(int coff, int k) {
+  if constexpr (VEC == 8) return coff + 8 > k ? 4 : 8;
+  else return VEC;
+}
+template <int VEC>
+__device__ __forceinline__ void store_row_vec(float* p, const float (&v)[VEC], int nval, uint64_t pol) {
+  if constexpr (VEC == 8) {
+    const float lo[4] = {v[0], v[1], v[2], v[3]}, hi[4] = {v[4], v[5], v[6], v[7]};
+    store_vec<4>(p, lo, pol);
+    if (nval == 8) store_vec<4>(p + 4, hi, pol);
+  } else {
+    store_vec<VEC>(p, v, pol);
+  }
+}
+template <int VEC>
+__device__ __forceinline__ void store_row_vec(float* p, const float (&v)[VEC], int nval) {
+  if constexpr (VEC == 8) {
+    const float lo[4] = {v[0], v[1], v[2], v[3]}, hi[4] = {v[4], v[5], v[6], v[7]};
+    store_vec<4>(p, lo);
+    if (nval == 8) store_vec<4>(p + 4, hi);
+  } else {
+    store_vec<VEC>(p, v);
   }
 }
 
@@ -662,13 +712,15 @@ spmm_stream_kernel(const Seg* __restrict__ segs, int n_segs, const int32_t* __re
     for (int t = 0; t < NV; ++t) {
       if (cok[t]) {
         float o[VEC];
+        const int nval = cols_valid<VEC>(coff[t], k);
         if (epi & GCNB_EPI_ACCUM) {
 #pragma unroll
-          for (int x = 0; x < VEC; ++x) acc[t][x] += crow[coff[t] + x];
+          for (int x = 0; x < VEC; ++x)
+            if (x < nval) acc[t][x] += crow[coff[t] + x];
         }
 #pragma unroll
-        for (int x = 0; x < VEC; ++x) o[x] = epilogue(acc[t][x], bias, coff[t] + x, epi);
-        store_vec<VEC>(crow + coff[t], o, pol_s);
+        for (int x = 0; x < VEC; ++x) o[x] = epilogue(acc[t][x], bias, VEC == 8 ? min(coff[t] + x, k - 1) : coff[t] + x, epi);
+        store_row_vec<VEC>(crow + coff[t], o, nval, pol_s);
       }
 #pragma unroll
       for (int x = 0; x < VEC; ++x) acc[t][x] = 0.f;
@@ -801,7 +853,11 @@ __global__ void __launch_bounds__(kStreamWarps * 32, MINB)
 spmm_stream_packed_kernel(const Seg* __restrict__ segs, int n_segs, const int32_t* __restrict__ rowptr,
                           const int2* __restrict__ cv, const TB* __restrict__ B, uint32_t ldb_bytes,
                           float* __restrict__ C, int64_t ldc, float* __restrict__ partials, int k,
-                          const float* __restrict__ bias, int epi_arg) {
+                          const float* __restrict__ bias, int epi_l2) {
+  // bits 8.. of the last argument: L2 eviction priorities, as in spmm_stream_kernel
+  const int epi_arg = epi_l2 & 0xff;
+  const uint64_t pol_s = l2_policy((epi_l2 & kL2Streams) ? 1 : 0);
+  const uint64_t pol_b = l2_policy((epi_l2 & kL2BLast) ? 2 : 0);
   constexpr int L = 32 / S;     // lanes per sub-group
   constexpr int BLK = U * S;    // non-zeros per ring turn
   static_assert(S >= 2 && 32 % BLK == 0, "a ring turn must not straddle a slab");
@@ -838,13 +894,15 @@ spmm_stream_packed_kernel(const Seg* __restrict__ segs, int n_segs, const int32_
       float* crow = r1s < 0 ? partials + (int64_t)(-1 - r1s) * k : C + (int64_t)row * ldc;
       const int epi = r1s < 0 ? 0 : epi_arg;
       float o[VEC];
+      const int nval = cols_valid<VEC>(coff, k);
       if (epi & GCNB_EPI_ACCUM) {
 #pragma unroll
-        for (int x = 0; x < VEC; ++x) acc[x] += crow[coff + x];
+        for (int x = 0; x < VEC; ++x)
+          if (x < nval) acc[x] += crow[coff + x];
       }
 #pragma unroll
-      for (int x = 0; x < VEC; ++x) o[x] = epilogue(acc[x], bias, coff + x, epi);
-      store_vec<VEC>(crow + coff, o);
+      for (int x = 0; x < VEC; ++x) o[x] = epilogue(acc[x], bias, VEC == 8 ? min(coff + x, k - 1) : coff + x, epi);
+      store_row_vec<VEC>(crow + coff, o, nval, pol_s);
     }
 #pragma unroll
     for (int x = 0; x < VEC; ++x) acc[x] = 0.f;
@@ -883,26 +941,26 @@ spmm_stream_packed_kernel(const Seg* __restrict__ segs, int n_segs, const int32_
   const uint32_t slab_s = slab_a + 8u * (uint32_t)sub;   // this sub-group's entry inside a slot
   const int2* src = cv + z0;
   int2 e = make_int2(0, 0);
-  if (lane < total) e = ld_stream_int2(src + lane);
+  if (lane < total) e = ld_stream_int2(src + lane, pol_s);
   auto refill = [&](int at) {
     __syncwarp();
     asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(slab_l), "r"(e.x), "r"(e.y) : "memory");
     __syncwarp();
-    if (at + 32 + lane < total) e = ld_stream_int2(src + at + 32 + lane);
+    if (at + 32 + lane < total) e = ld_stream_int2(src + at + 32 + lane, pol_s);
   };
   // slot u <- non-zeros at .. at+S-1 (at is a multiple of S), one per sub-group
   auto issue_full = [&](int u, int at) {
     int2 q;
     asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(q.x), "=r"(q.y) : "r"(slab_s + 8u * (uint32_t)(at & 31)) : "memory");
     av[u] = __int_as_float(q.y);
-    if (cok) bv[u].load(reinterpret_cast<const TB*>(bl + (uint64_t)(uint32_t)q.x * ldb_bytes));
+    if (cok) bv[u].load(reinterpret_cast<const TB*>(bl + (uint64_t)(uint32_t)q.x * ldb_bytes), pol_b);
   };
   auto issue_tail = [&](int u, int at) {
     int2 q;
     asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(q.x), "=r"(q.y) : "r"(slab_s + 8u * (uint32_t)(at & 31)) : "memory");
     const bool valid = at + sub < total;   // entries past the end of the stream are stale
     av[u] = valid ? __int_as_float(q.y) : 0.f;
-    if (valid && cok) bv[u].load(reinterpret_cast<const TB*>(bl + (uint64_t)(uint32_t)q.x * ldb_bytes));
+    if (valid && cok) bv[u].load(reinterpret_cast<const TB*>(bl + (uint64_t)(uint32_t)q.x * ldb_bytes), pol_b);
     else bv[u].zero();
   };
 

@@ -32,6 +32,8 @@ Two ways of bringing the remote rows in (``exchange=``):
 """
 from __future__ import annotations
 
+import os
+
 import numpy as np
 import torch
 import torch.distributed as dist
@@ -163,6 +165,57 @@ class _PeerExchange:
             self.own_ptr = None
 
 
+class _PeerFlags:
+    """One array of `world` uint32 words per rank in peer-mapped memory, for gcnb_peer_barrier.  Collective to
+    construct: the words are zeroed BEFORE the handles travel, so no peer can write into an array that its owner
+    has yet to clear."""
+
+    def __init__(self, device, group):
+        import ctypes
+        from . import _ffi
+        self._ffi, self._ct = _ffi, ctypes
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self.device = device
+        ptr = ctypes.c_void_p()
+        handle = (ctypes.c_ubyte * 64)()
+        _ffi.call("gcnb_peer_alloc", device.index, 256, ctypes.byref(ptr), handle)
+        self.own_ptr = ptr.value
+
+        class _Raw:
+            pass
+        raw = _Raw()
+        raw.__cuda_array_interface__ = {"shape": (64,), "typestr": "<i4", "data": (self.own_ptr, False),
+                                        "version": 2, "strides": None}
+        torch.as_tensor(raw, device=device).zero_()
+        torch.cuda.synchronize(device)
+        handles = [None] * self.world
+        dist.all_gather_object(handles, bytes(handle), group=group)
+        self.base, self._opened = [], []
+        for q, h in enumerate(handles):
+            if q == self.rank:
+                self.base.append(self.own_ptr)
+                continue
+            p = ctypes.c_void_p()
+            _ffi.call("gcnb_peer_open", device.index, (ctypes.c_ubyte * 64).from_buffer_copy(h), ctypes.byref(p))
+            self.base.append(p.value)
+            self._opened.append(p.value)
+        self.bases = (ctypes.c_void_p * self.world)(*self.base)
+        self.epoch = 0
+
+    def barrier(self, stream):
+        self.epoch = (self.epoch + 1) & 0xFFFFFFFF
+        self._ffi.call("gcnb_peer_barrier", self.bases, self.world, self.rank, self._ct.c_uint32(self.epoch),
+                       self._ct.c_void_p(stream.cuda_stream))
+
+    def close(self):
+        for p in self._opened:
+            self._ffi.lib.gcnb_peer_close(self.device.index, self._ct.c_void_p(p))
+        self._opened = []
+        if self.own_ptr:
+            self._ffi.lib.gcnb_peer_free(self.device.index, self._ct.c_void_p(self.own_ptr))
+            self.own_ptr = None
+
+
 class PartitionedSpMM:
     """Row block `rank` of Â (and of Âᵀ unless symmetric) prepared for the gathered SpMM."""
 
@@ -204,6 +257,13 @@ class PartitionedSpMM:
         # exchange stream: high priority, so that its (few, short) CTAs are scheduled between the
         # CTAs of the local-block SpMM that fills the machine at the same time
         self._side = torch.cuda.Stream(self.device, priority=-1) if self.device.type == "cuda" else None
+        # rendezvous of the ranks: flags in peer memory (one small kernel, gcnb_peer_barrier) when the ranks sit on
+        # different GPUs of one box (NCCL group); a one-element all-reduce otherwise (gloo: CPU tests, and the GPU
+        # tests that put two ranks on one device, where a spinning kernel would wait for a time slice)
+        self._peer_flags = None
+        if (self.exchange == "pull" and self.device.type == "cuda" and self.world > 1
+                and dist.get_backend(group) == "nccl" and os.environ.get("GCNB_FLAG_BARRIER", "1") != "0"):
+            self._peer_flags = _PeerFlags(self.device, group)
 
     def _make_blocks(self, rowptr, col, val):
         local, remote, stride = split_local_remote(rowptr, col, val, self.bounds, self.rank)
@@ -278,7 +338,11 @@ class PartitionedSpMM:
         return slot
 
     def _rank_barrier(self):
-        """Stream-ordered rendezvous of all ranks (a one-element all-reduce on the current stream)."""
+        """Stream-ordered rendezvous of all ranks on the current stream: flags in peer memory
+        (gcnb_peer_barrier) between the GPUs of one box, else a one-element all-reduce."""
+        if self._peer_flags is not None:
+            self._peer_flags.barrier(torch.cuda.current_stream(self.device))
+            return
         if self._flag is None:
             self._flag = torch.zeros(1, dtype=torch.float32, device=self.device)
         dist.all_reduce(self._flag, group=self.group)
@@ -321,6 +385,9 @@ class PartitionedSpMM:
         for ex in self._exchanges.values():
             ex.close()
         self._exchanges = {}
+        if self._peer_flags is not None:
+            self._peer_flags.close()
+            self._peer_flags = None
 
     def _apply(self, blocks, B_local: torch.Tensor) -> torch.Tensor:
         if B_local.shape[0] != self.m_local:

@@ -185,6 +185,15 @@ int gcnb_peer_close(int device, void* ptr);
 int gcnb_pull_rows(const void* const* bases, int n_parts, int64_t src_pitch_bytes,
                    const int32_t* part, const int32_t* row, void* out, int64_t out_pitch_bytes,
                    int64_t n_rows, int64_t row_bytes, int64_t first_row, void* stream);
+/* Stream-ordered rendezvous of the ranks through flags in peer memory (replaces a one-element NCCL all-reduce,
+ * which costs ~0.11 ms per SpMM on the critical path, profiles/r02_ah_*).  Every rank owns an array of n_parts
+ * uint32 words in a gcnb_peer_alloc'ed buffer, zeroed before first use and mapped on the peers; flag_bases is a
+ * HOST array of those n_parts device pointers as seen from THIS process.  The call enqueues one small kernel:
+ * it publishes `epoch` into this rank's word of every peer's array (release, system scope) and waits until every
+ * peer's word in the rank's own array has reached `epoch`.  All ranks pass the same, growing epoch (1, 2, ...).
+ * Work enqueued on `stream` before the call is visible to peers that pass the rendezvous; work after it starts
+ * when every rank has arrived.  A peer that never arrives makes the kernel trap after ~10 s. */
+int gcnb_peer_barrier(const void* const* flag_bases, int n_parts, int rank, uint32_t epoch, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Host graph preprocessing (bit-exact with the reference).  All arrays HOST memory.

@@ -167,6 +167,44 @@ def test_cuda_graph_step_matches_eager(golden_gcn):
     assert rel_err(losses[True][1], losses[False][1]) < 1e-4
 
 
+@pytest.mark.parametrize("assoc", ["reference", "auto"])
+def test_training_trajectory_matches_reference_epochs(golden_gcn, assoc):
+    """20 epochs of GCN.fit's loop (_train_without_val: zero_grad, forward, NLL on idx_train, backward, Adam with
+    weight decay) against the CPU restatement of the reference's epoch (oracle gcn_epoch_cpu: pygcn/gcn1.py:62-118,
+    :176-203 with torch.spmm on the host), dropout off, same initial weights.  Adam divides by sqrt(v), so a
+    last-bit difference in a tiny gradient moves that weight by up to lr: the bound is on the loss of every epoch
+    (1e-4 relative) and on the weights after 20 epochs (2e-3 of their scale), not the single-step 1e-5."""
+    from oracle import spmm_oracle as SO
+    g = golden_gcn
+    n, a, _ = _load(g)
+    rng = np.random.default_rng(11)
+    X = rng.standard_normal((n, 24)).astype(np.float32)
+    labels = rng.integers(0, 7, n)
+    idx = np.arange(0, n, 2)
+    torch.manual_seed(3)
+    m = model.GCN(nfeat=24, nhid=16, nclass=7, dropout=0.0, device=DEV, association=assoc)
+    m.initialize()
+    init = [p.detach().cpu().clone() for p in (m.gc1.weight, m.gc1.bias, m.gc2.weight, m.gc2.bias)]
+    # the reference side, on the host
+    an = graph.normalize_adj(a).tocsr()
+    adj_coo = SO.torch_coo(an.indptr, an.indices, an.data, an.shape)
+    params = [p.clone().requires_grad_(True) for p in init]
+    opt = torch.optim.Adam(params, lr=0.01, weight_decay=5e-4)
+    xt, lt, it = torch.from_numpy(X), torch.from_numpy(labels), torch.from_numpy(idx)
+    ref_losses = [float(SO.gcn_epoch_cpu(adj_coo, xt, lt, it, params, opt, dropout=0.0).detach()) for _ in range(20)]
+    # ours: the same loop fit() runs, one epoch at a time so that every loss is seen
+    m.features, m.adj_norm, m.labels, m.vomp = m._prepare(xt, a, labels, True, None)
+    m._ax_cache = None
+    idx_d = m._map_index(idx)
+    optimizer = torch.optim.Adam(m.parameters(), lr=m.lr, weight_decay=m.weight_decay)
+    losses = [float(m._step(optimizer, m.labels, idx_d)[1].detach()) for _ in range(20)]
+    assert ref_losses[-1] < ref_losses[0]          # it trains
+    for e, (x, y) in enumerate(zip(losses, ref_losses)):
+        assert abs(x - y) <= 1e-4 * abs(y), (e, x, y)
+    for ours, ref in zip((m.gc1.weight, m.gc1.bias, m.gc2.weight, m.gc2.bias), params):
+        assert rel_err(ours.detach().cpu().numpy(), ref.detach().numpy()) < 2e-3
+
+
 def test_fused_logsoftmax_nll_matches_torch():
     """ops.logsoftmax_nll (gcnb_logsoftmax_nll_fwd/bwd) against F.log_softmax + F.nll_loss and their autograd,
     with padding columns in the logits (the aggregation runs at a multiple of 4 columns) and a custom divisor."""

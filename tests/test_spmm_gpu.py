@@ -328,6 +328,41 @@ def test_packed_stream_kernel_narrow_widths(k):
     assert rel_err(plan.spmm(Bp, out=Cp).cpu().numpy(), ref) < FP32_TOL
 
 
+@pytest.mark.parametrize("k", [4, 8, 12, 28, 32, 36, 60, 64, 68, 100, 104, 128, 132, 200, 256, 260, 512, 602])
+@pytest.mark.parametrize("dense", [True, False])
+def test_f32_rows_at_32_byte_pitch(k, dense):
+    """fp32 feature rows whose pitch is a multiple of 8 floats (32-byte aligned rows): the shapes the 256-bit
+    load kernels take (spmm.cu launch_vec8: packed S = 8/4/2 up to k = 128 on dense-row graphs, stream NV = 1/2
+    beyond; k % 8 == 4 leaves the last lane 4 real and 4 padding columns).  Padding columns of C must stay
+    untouched, epilogues and accumulate as everywhere else, bit-reproducible."""
+    A = _dense_skew_graph() if dense else random_normalized_graph(900, 9000, k, "skew")
+    n = A.shape[0]
+    rng = np.random.default_rng(500 + k)
+    B = rng.standard_normal((n, k)).astype(np.float32)
+    bias = rng.standard_normal(k).astype(np.float32)
+    ref = SO.spmm_f64(A.indptr, A.indices, A.data, n, B)
+    plan = ops.SpmmPlan.from_scipy(A, device=DEV)
+    pitch = (k + 7) // 8 * 8
+    for extra in (0, 8):
+        Bfull = torch.full((n, pitch + extra), 1e30, device=DEV)      # poison in the padding: must never reach C
+        Bp = Bfull[:, :k]
+        Bp.copy_(torch.from_numpy(B))
+        Cfull = torch.full((n, pitch + extra), -7.0, device=DEV)
+        Cp = Cfull[:, :k]
+        out = plan.spmm(Bp, out=Cp)
+        assert rel_err(out.cpu().numpy(), ref) < FP32_TOL
+        assert bool((Cfull[:, k:] == -7.0).all()), "padding columns of C were written"
+        again = torch.full((n, pitch + extra), -7.0, device=DEV)[:, :k]
+        assert torch.equal(plan.spmm(Bp, out=again), out)
+        Ce = torch.empty(n, pitch + extra, device=DEV)[:, :k]
+        plan.spmm(Bp, out=Ce, bias=torch.from_numpy(bias).to(DEV), relu=True)
+        assert rel_err(Ce.cpu().numpy(), np.maximum(ref + bias, 0)) < FP32_TOL
+        C0 = torch.zeros(n, pitch + extra, device=DEV)[:, :k]
+        C0.copy_(torch.from_numpy(B))
+        want = B.astype(np.float64) + ref
+        assert rel_err(plan.spmm(Bp, out=C0, accumulate=True).cpu().numpy(), want) < FP32_TOL
+
+
 # ---- panel class (32-row panels walking their columns in step; spmm_panel_kernel) -----------------
 def _hub_graph(n, e, seed):
     """Skewed rows AND columns: the first panels are nearly dense (they get cut into several items whose

@@ -1,7 +1,7 @@
 #!/bin/bash
-# round 2, GPU batch ac: source-level profile of the packed stream kernel at k = 48 (half of the products epoch) and
+# round 2, GPU batch ae: source-level profile of the packed stream kernel at k = 48 (half of the products epoch) and
 # of the stream kernel at k = 100 (the headline): where do the instructions go?
-tag=${1:-r02_ac}; o=gpurun_out; mkdir -p $o
+tag=${1:-r02_ae}; o=gpurun_out; mkdir -p $o
 for k in 48 100; do
   CMD="python bench.py --k $k --steps 2 --warmup 1 --comparators none --no-epoch"
   $CMD > $o/${tag}_plain_k$k.log 2>&1 && timeout 900 ncu --set full --clock-control none --import-source on -k regex:spmm_stream -s 1 -c 1 -f -o /tmp/prof_k$k $CMD > $o/${tag}_ncu_k$k.log 2>&1
