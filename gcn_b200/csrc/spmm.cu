@@ -367,7 +367,8 @@ static void launch_stream_cfg(const LaunchArgs& a, int64_t gs, unsigned ytiles) 
   const Matrix& M = *a.M;
   // GCNB_L2POL: bit 0 = (col,val) stream and C rows evict_first, bit 1 = feature rows evict_last
   static const int l2pol = getenv("GCNB_L2POL") ? atoi(getenv("GCNB_L2POL")) : 1;
-  const int l2 = ((l2pol & 1) ? kL2Streams : 0) | ((l2pol & 2) ? kL2BLast : 0);
+  static const int medium = getenv("GCNB_PACKED_MEDIUM") ? atoi(getenv("GCNB_PACKED_MEDIUM")) : 1;
+  const int l2 = ((l2pol & 1) ? kL2Streams : 0) | ((l2pol & 2) ? kL2BLast : 0) | (medium ? 0 : kNoMedium);
   spmm_stream_kernel<TB, VEC, NV, U, MINB><<<dim3((unsigned)gs, ytiles), kStreamWarps * 32, 0, a.stream>>>(
       M.segs, (int)M.n_segs, M.rowptr, M.cv, (const TB*)a.B, (uint32_t)(a.ldb * sizeof(TB)), a.C, a.ldc,
       a.partials, a.k, a.bias, a.epi | l2);
@@ -498,7 +499,8 @@ static int launch_packed(const LaunchArgs& a) {
   if (gs > 0x7fffffffLL || a.ldb * (int64_t)sizeof(TB) > 0xffffffffLL)
     return set_error(GCNB_ERR_UNSUPPORTED, "matrix too large for one grid");
   static const int l2pol = getenv("GCNB_L2POL") ? atoi(getenv("GCNB_L2POL")) : 1;
-  const int l2 = ((l2pol & 1) ? kL2Streams : 0) | ((l2pol & 2) ? kL2BLast : 0);
+  static const int medium = getenv("GCNB_PACKED_MEDIUM") ? atoi(getenv("GCNB_PACKED_MEDIUM")) : 1;
+  const int l2 = ((l2pol & 1) ? kL2Streams : 0) | ((l2pol & 2) ? kL2BLast : 0) | (medium ? 0 : kNoMedium);
   if constexpr (sizeof(TB) == 4 && VEC == 8) {
     // 256-bit loads: a ring slot is 8 registers.  GCNB_PACKED_CFG picks ring depth / CTAs per SM (experiments)
     static const int pcfg = getenv("GCNB_PACKED_CFG") ? atoi(getenv("GCNB_PACKED_CFG")) : 0;

@@ -626,6 +626,7 @@ spmm_warp_row_kernel(const int32_t* __restrict__ rowptr, const int2* __restrict_
 constexpr int kStreamWarps = 4;
 constexpr int kL2Streams = 0x100;   // stream-kernel argument bits above the GCNB_EPI_* flags
 constexpr int kL2BLast = 0x200;
+constexpr int kNoMedium = 0x400;   // packed kernel: row ends inside a turn take the general path only (experiments)
 constexpr int kSegNnz = 768;     // target non-zeros per segment of short rows (plan time)
 constexpr int kSegLong = 1024;   // a long row is cut into pieces of at most this many non-zeros
 
@@ -645,7 +646,10 @@ spmm_stream_kernel(const Seg* __restrict__ segs, int n_segs, const int32_t* __re
                    const float* __restrict__ bias, int epi_l2) {
   // ring depths that divide 32 never straddle a 32-entry slab; others (U = 3: the measured per-warp cap on
   // gathers in flight) use a circular slab of two 32-entry halves
-  constexpr int SL = (32 % U == 0) ? 32 : 64;
+  // The slab is a ring of four 32-entry quarters filled by cp.async two quarters ahead of the one being issued
+  // from: no register holds the (col,val) stream in flight (the register version stalled 5 % of the warp time
+  // on its shared-memory store, profiles/r02_ae_*) and a ring turn may straddle two quarters (U = 3).
+  constexpr int SL = 128;
   // bits 8.. of the last argument: L2 eviction priorities (kL2Streams: (col,val) stream and C rows are
   // evict_first; kL2BLast: gathered feature rows are evict_last), chosen by the host (spmm.cu)
   const int epi_arg = epi_l2 & 0xff;
@@ -668,7 +672,10 @@ spmm_stream_kernel(const Seg* __restrict__ segs, int n_segs, const int32_t* __re
     coff[t] = colbase + (lane + t * 32) * VEC;
     cok[t] = coff[t] < k;
   }
-  const char* bl = reinterpret_cast<const char*>(B + (cok[0] ? coff[0] : 0));
+  // NV == 1: lanes past the row's last vector point at that last vector and load without a predicate (the bytes
+  // sit in the 128-byte line their quarter-warp touches anyway; their sums are never stored)
+  const char* bl = reinterpret_cast<const char*>(
+      B + (cok[0] ? coff[0] : (NV == 1 ? colbase + ((k - 1 - colbase) / VEC) * VEC : 0)));
   const int r1s = sg.y;
 
   // row ends of rows rbase .. rbase+31, one per lane
@@ -766,20 +773,23 @@ spmm_stream_kernel(const Seg* __restrict__ segs, int n_segs, const int32_t* __re
   const int2* src = cv + z0;
   // issue side: `nxt` = stream position of the next non-zero to gather; its slab is refilled whenever
   // nxt crosses a multiple of 32 (every earlier entry of the old slab has been issued by then)
-  int2 e = make_int2(0, 0);
-  if (lane < total) e = ld_stream_int2(src + lane, pol_s);
-  auto refill = [&](int at) {   // make slab hold stream positions [at, at+32) (at: multiple of 32)
+  auto prefetch = [&](int at) {   // quarter (at / 32) % 4 <- stream positions [at, at+32), asynchronously
+    if (at + lane < total)
+      asm volatile("cp.async.ca.shared.global.L2::cache_hint [%0], [%1], 8, %2;"
+                   ::"r"(slab_l + 8u * (uint32_t)(at & (SL - 32))), "l"(src + at + lane), "l"(pol_s) : "memory");
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  auto refill = [&](int at) {   // positions [at, at+32) become readable (at: multiple of 32); [at+64, at+96) starts
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
     __syncwarp();
-    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(slab_l + 8u * (uint32_t)(at & (SL - 32))), "r"(e.x), "r"(e.y) : "memory");
-    __syncwarp();
-    if (at + 32 + lane < total) e = ld_stream_int2(src + at + 32 + lane, pol_s);
+    prefetch(at + 64);
   };
   auto gather = [&](int u, int c, int vbits) {
     av[u] = __int_as_float(vbits);
     const char* p0 = bl + (uint64_t)(uint32_t)c * ldb_bytes;
 #pragma unroll
     for (int t = 0; t < NV; ++t)
-      if (cok[t]) bv[u][t].load(reinterpret_cast<const TB*>(p0) + t * 32 * VEC, pol_b);
+      if (NV == 1 || cok[t]) bv[u][t].load(reinterpret_cast<const TB*>(p0) + t * 32 * VEC, pol_b);
   };
   auto issue = [&](int u, int at) {   // gather non-zero `at` (valid) into ring slot u
     int2 q;
@@ -789,23 +799,52 @@ spmm_stream_kernel(const Seg* __restrict__ segs, int n_segs, const int32_t* __re
   auto issue2 = [&](int u, int at) {   // two consecutive non-zeros (at even) with one LDS.128 broadcast
     int4 q;
     asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(q.x), "=r"(q.y), "=r"(q.z), "=r"(q.w)
-                 : "r"(slab_a + 8u * (uint32_t)(at & 31)) : "memory");
+                 : "r"(slab_a + 8u * (uint32_t)(at & (SL - 1))) : "memory");
+    gather(u, q.x, q.y);
+    gather(u + 1, q.z, q.w);
+  };
+
+  auto issue2_at = [&](int u, uint32_t addr) {   // the same from a ready-made slab address
+    int4 q;
+    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(q.x), "=r"(q.y), "=r"(q.z), "=r"(q.w) : "r"(addr) : "memory");
     gather(u, q.x, q.y);
     gather(u + 1, q.z, q.w);
   };
 
   // prologue: fill the ring
+  prefetch(0);
+  prefetch(32);
   refill(0);
 #pragma unroll
   for (int u = 0; u < U; ++u)
     if (u < total) issue(u, u);
 
   for (int g = 0; g < total; g += U) {   // consume [g, g+U), issue [g+U, g+2U)
+    if constexpr (32 % U == 0 && U % 2 == 0) {
+      if (!(epi_l2 & kNoMedium) && (g & 31) == 0 && g + 32 <= rend && g + 32 + U <= total) {
+        // a whole quarter without a row end, the turn after it complete: its 32 / U turns in one piece, slab
+        // offsets constant, no per-turn tests
+        const uint32_t qa = slab_a + 8u * (uint32_t)(g & (SL - 32));
+        const uint32_t qb = slab_a + 8u * (uint32_t)((g + 32) & (SL - 32));
+#pragma unroll
+        for (int t = 1; t <= 32 / U; ++t) {
+          if (t == 32 / U) refill(g + 32);
+#pragma unroll
+          for (int u = 0; u < U; u += 2) {
+            consume(u);
+            consume(u + 1);
+            issue2_at(u, (t < 32 / U ? qa + 8u * (uint32_t)(t * U + u) : qb + 8u * (uint32_t)u));
+          }
+        }
+        g += 32 - U;
+        continue;
+      }
+    }
     const int nxt = g + U;
-    if constexpr (SL == 32) {
+    if constexpr (32 % U == 0) {
       if ((nxt & 31) == 0 && nxt < total) refill(nxt);
     } else {
-      // the group issued in this turn is [nxt, nxt+U): store its 32-entry chunk when it starts one
+      // the group issued in this turn is [nxt, nxt+U): make its quarter readable when it starts one
       const int last = nxt + U - 1;
       if ((last >> 5) != ((nxt - 1) >> 5) && (last & ~31) < total) refill(last & ~31);
     }
@@ -858,10 +897,14 @@ spmm_stream_packed_kernel(const Seg* __restrict__ segs, int n_segs, const int32_
   const int epi_arg = epi_l2 & 0xff;
   const uint64_t pol_s = l2_policy((epi_l2 & kL2Streams) ? 1 : 0);
   const uint64_t pol_b = l2_policy((epi_l2 & kL2BLast) ? 2 : 0);
+  const bool medium = !(epi_l2 & kNoMedium);
   constexpr int L = 32 / S;     // lanes per sub-group
   constexpr int BLK = U * S;    // non-zeros per ring turn
   static_assert(S >= 2 && 32 % BLK == 0, "a ring turn must not straddle a slab");
-  __shared__ alignas(16) int2 s_cv[kStreamWarps][32];
+  // (col,val) slab: four 32-entry quarters per warp, filled by cp.async two quarters ahead of the one being issued
+  // from — no register holds the stream in flight and the copy has ~16 ring turns to arrive
+  constexpr int SLQ = 128;
+  __shared__ alignas(16) int2 s_cv[kStreamWarps][SLQ];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int s = blockIdx.x * kStreamWarps + warp;
   if (s >= n_segs) return;
@@ -873,7 +916,9 @@ spmm_stream_packed_kernel(const Seg* __restrict__ segs, int n_segs, const int32_
   const int r1s = sg.y;
   const int coff = li * VEC;
   const bool cok = coff < k;
-  const char* bl = reinterpret_cast<const char*>(B + (cok ? coff : 0));
+  // lanes past the row's last vector point at that last vector: their (unpredicated) loads stay inside the
+  // 128-byte line their quarter-warp touches anyway
+  const char* bl = reinterpret_cast<const char*>(B + (cok ? coff : ((k - 1) / VEC) * VEC));
 
   int rbase = row;
   const int z0 = sg.z;
@@ -940,43 +985,102 @@ spmm_stream_packed_kernel(const Seg* __restrict__ segs, int n_segs, const int32_
   asm volatile("mov.u32 %0, %1;" : "=r"(slab_l) : "r"(slab_a + 8u * (uint32_t)lane));
   const uint32_t slab_s = slab_a + 8u * (uint32_t)sub;   // this sub-group's entry inside a slot
   const int2* src = cv + z0;
-  int2 e = make_int2(0, 0);
-  if (lane < total) e = ld_stream_int2(src + lane, pol_s);
+  // quarter (at / 32) % 4 <- stream positions [at, at+32), asynchronously (lanes past the end copy nothing:
+  // their entries are never read as valid)
+  auto prefetch = [&](int at) {
+    if (at + lane < total)
+      asm volatile("cp.async.ca.shared.global.L2::cache_hint [%0], [%1], 8, %2;"
+                   ::"r"(slab_l + 8u * (uint32_t)(at & (SLQ - 32))), "l"(src + at + lane), "l"(pol_s) : "memory");
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  // make positions [at, at+32) readable (their copy was committed two refills ago) and start the copy of
+  // [at+64, at+96) into the quarter that held [at-64, at-32), which nothing reads any more
   auto refill = [&](int at) {
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
     __syncwarp();
-    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(slab_l), "r"(e.x), "r"(e.y) : "memory");
-    __syncwarp();
-    if (at + 32 + lane < total) e = ld_stream_int2(src + at + 32 + lane, pol_s);
+    prefetch(at + 64);
   };
   // slot u <- non-zeros at .. at+S-1 (at is a multiple of S), one per sub-group
   auto issue_full = [&](int u, int at) {
     int2 q;
-    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(q.x), "=r"(q.y) : "r"(slab_s + 8u * (uint32_t)(at & 31)) : "memory");
+    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(q.x), "=r"(q.y) : "r"(slab_s + 8u * (uint32_t)(at & (SLQ - 1))) : "memory");
     av[u] = __int_as_float(q.y);
-    if (cok) bv[u].load(reinterpret_cast<const TB*>(bl + (uint64_t)(uint32_t)q.x * ldb_bytes), pol_b);
+    // lanes past the row's last vector (cok false) re-read that last vector (see `bl`), so the load needs no
+    // predicate; their sums are never stored
+    bv[u].load(reinterpret_cast<const TB*>(bl + (uint64_t)(uint32_t)q.x * ldb_bytes), pol_b);
+  };
+  // the same from a slab address (of this sub-group's entry of the turn's first slot) plus a byte offset that is a
+  // compile-time constant after unrolling: one address computation per turn instead of one per slot
+  auto issue_slab = [&](int u, uint32_t sa, uint32_t off) {
+    int2 q;
+    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(q.x), "=r"(q.y) : "r"(sa + off) : "memory");
+    av[u] = __int_as_float(q.y);
+    bv[u].load(reinterpret_cast<const TB*>(bl + (uint64_t)(uint32_t)q.x * ldb_bytes), pol_b);
   };
   auto issue_tail = [&](int u, int at) {
     int2 q;
-    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(q.x), "=r"(q.y) : "r"(slab_s + 8u * (uint32_t)(at & 31)) : "memory");
+    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(q.x), "=r"(q.y) : "r"(slab_s + 8u * (uint32_t)(at & (SLQ - 1))) : "memory");
     const bool valid = at + sub < total;   // entries past the end of the stream are stale
     av[u] = valid ? __int_as_float(q.y) : 0.f;
     if (valid && cok) bv[u].load(reinterpret_cast<const TB*>(bl + (uint64_t)(uint32_t)q.x * ldb_bytes), pol_b);
     else bv[u].zero();
   };
 
+  prefetch(0);
+  prefetch(32);
   refill(0);
 #pragma unroll
   for (int u = 0; u < U; ++u)
     if (u * S < total) issue_tail(u, u * S);
 
   for (int g = 0; g < total; g += BLK) {
+    if (medium && (g & 31) == 0 && g + 32 <= rend && g + 32 + BLK <= total) {
+      // a whole slab without a row end, and the turn after it complete: its 32 / BLK turns in one piece — slab
+      // offsets are constants, no per-turn tests (about half of all non-zeros at 50 per row)
+      const uint32_t qa = slab_s + 8u * (uint32_t)(g & (SLQ - 32));              // quarter of [g, g+32)
+      const uint32_t qb = slab_s + 8u * (uint32_t)((g + 32) & (SLQ - 32));       // the one after it
+#pragma unroll
+      for (int t = 1; t <= 32 / BLK; ++t) {
+        if (t == 32 / BLK) refill(g + 32);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          consume(u);
+          if (t < 32 / BLK) issue_slab(u, qa, 8u * (uint32_t)(t * BLK + u * S));
+          else issue_slab(u, qb, 8u * (uint32_t)(u * S));
+        }
+      }
+      g += 32 - BLK;
+      continue;
+    }
     const int nxt = g + BLK;
     if ((nxt & 31) == 0 && nxt < total) refill(nxt);
     if (nxt <= rend && nxt + BLK <= total) {
       // fast path: no row end inside this turn, the next turn is complete
+      const uint32_t sa = slab_s + 8u * (uint32_t)(nxt & (SLQ - 1));
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         consume(u);
+        issue_slab(u, sa, 8u * (uint32_t)(u * S));
+      }
+    } else if (medium && nxt + BLK <= total) {
+      // a row ends inside this turn, the next turn is complete (every turn but a segment's last two): slots the
+      // row end does not touch are consumed whole, the next turn is issued without validity tests
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int base = g + u * S;
+        if (rend >= base + S) {
+          consume(u);
+        } else {
+          const int pos = base + sub;
+          int done = base;
+          while (true) {
+            while (done == rend) flush();
+            const int lim = min(rend, base + S);
+            if (pos >= done && pos < lim) consume(u);
+            done = lim;
+            if (done >= base + S) break;
+          }
+        }
         issue_full(u, nxt + u * S);
       }
     } else {
