@@ -826,15 +826,23 @@ spmm_stream_kernel(const Seg* __restrict__ segs, int n_segs, const int32_t* __re
         // offsets constant, no per-turn tests
         const uint32_t qa = slab_a + 8u * (uint32_t)(g & (SL - 32));
         const uint32_t qb = slab_a + 8u * (uint32_t)((g + 32) & (SL - 32));
-#pragma unroll
-        for (int t = 1; t <= 32 / U; ++t) {
-          if (t == 32 / U) refill(g + 32);
+        // (rolled over the turns: fully unrolled, ptxas hoists the slab reads of all turns and spills around them)
+        uint32_t sa = qa + 8u * (uint32_t)U;
+#pragma unroll 1
+        for (int t = 1; t < 32 / U; ++t, sa += 8u * (uint32_t)U) {
 #pragma unroll
           for (int u = 0; u < U; u += 2) {
             consume(u);
             consume(u + 1);
-            issue2_at(u, (t < 32 / U ? qa + 8u * (uint32_t)(t * U + u) : qb + 8u * (uint32_t)u));
+            issue2_at(u, sa + 8u * (uint32_t)u);
           }
+        }
+        refill(g + 32);
+#pragma unroll
+        for (int u = 0; u < U; u += 2) {
+          consume(u);
+          consume(u + 1);
+          issue2_at(u, qb + 8u * (uint32_t)u);
         }
         g += 32 - U;
         continue;
@@ -1039,15 +1047,22 @@ spmm_stream_packed_kernel(const Seg* __restrict__ segs, int n_segs, const int32_
       // offsets are constants, no per-turn tests (about half of all non-zeros at 50 per row)
       const uint32_t qa = slab_s + 8u * (uint32_t)(g & (SLQ - 32));              // quarter of [g, g+32)
       const uint32_t qb = slab_s + 8u * (uint32_t)((g + 32) & (SLQ - 32));       // the one after it
-#pragma unroll
-      for (int t = 1; t <= 32 / BLK; ++t) {
-        if (t == 32 / BLK) refill(g + 32);
+      // (a rolled loop over the turns of the quarter: fully unrolled, ptxas hoists the slab reads of all turns
+      // and spills ring state around them)
+      uint32_t sa = qa + 8u * (uint32_t)BLK;
+#pragma unroll 1
+      for (int t = 1; t < 32 / BLK; ++t, sa += 8u * (uint32_t)BLK) {
 #pragma unroll
         for (int u = 0; u < U; ++u) {
           consume(u);
-          if (t < 32 / BLK) issue_slab(u, qa, 8u * (uint32_t)(t * BLK + u * S));
-          else issue_slab(u, qb, 8u * (uint32_t)(u * S));
+          issue_slab(u, sa, 8u * (uint32_t)(u * S));
         }
+      }
+      refill(g + 32);
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        consume(u);
+        issue_slab(u, qb, 8u * (uint32_t)(u * S));
       }
       g += 32 - BLK;
       continue;
