@@ -165,6 +165,9 @@ class _PeerExchange:
             self.own_ptr = None
 
 
+_LOCAL_AFTER_BARRIER = os.environ.get("GCNB_LOCAL_AFTER_BARRIER", "auto")   # "0", "1" or "auto"
+
+
 class _PeerFlags:
     """One array of `world` uint32 words per rank in peer-mapped memory, for gcnb_peer_barrier.  Collective to
     construct: the words are zeroed BEFORE the handles travel, so no peer can write into an array that its owner
@@ -260,6 +263,7 @@ class PartitionedSpMM:
         # rendezvous of the ranks: flags in peer memory (one small kernel, gcnb_peer_barrier) when the ranks sit on
         # different GPUs of one box (NCCL group); a one-element all-reduce otherwise (gloo: CPU tests, and the GPU
         # tests that put two ranks on one device, where a spinning kernel would wait for a time slice)
+        self._after_barrier = None
         self._peer_flags = None
         if (self.exchange == "pull" and self.device.type == "cuda" and self.world > 1
                 and dist.get_backend(group) == "nccl" and os.environ.get("GCNB_FLAG_BARRIER", "1") != "0"):
@@ -373,7 +377,29 @@ class PartitionedSpMM:
             return self._gathered(blocks, B_local)
         ex, slot = pre
         self._rank_barrier()
+        if self.device.type == "cuda":
+            if self._after_barrier is None:
+                self._after_barrier = torch.cuda.Event()
+            self._after_barrier.record(torch.cuda.current_stream(self.device))
         return self._pull(blocks, ex, slot, B_local.shape[1])
+
+    def _local_after_barrier(self, blocks, B_local) -> bool:
+        """Should the local block wait for the rendezvous kernel?  Launched first, it fills every SM and the
+        rendezvous takes 0.1-0.2 ms to get through instead of 0.01-0.02 (profiles/r02_ar_timeline_n2.jsonl) — which
+        matters when rendezvous + pull is the critical path (8 GPUs) and costs when the local block is (2 GPUs: it
+        runs 0.4 ms longer beside a pull that started with it).  'auto' compares rough estimates of the two: halo
+        bytes at 550 GB/s against local non-zeros at (5 + k/4) ps each, both measured on the products shape, and
+        waits when the pull is 1.3x longer (8 GPUs, profiles/r02_as_*: k = 100, ratio 1.4: step 1.14 -> 1.07 ms;
+        the epoch's k = 48 products, ratio 1.2: 2.85 -> 3.00 ms per epoch, so those do not wait)."""
+        if _LOCAL_AFTER_BARRIER in ("0", "1"):
+            return _LOCAL_AFTER_BARRIER == "1"
+        if self.exchange != "pull":
+            return False
+        k = B_local.shape[1]
+        esize = 2 if self.wire_dtype == torch.bfloat16 else 4
+        pull_s = blocks["halo_row"].numel() * k * esize / 550e9
+        local_s = int(blocks["local_csr"][0][-1]) * (5.0 + 0.25 * k) * 1e-12
+        return pull_s > 1.3 * local_s
 
     def _prepare(self, B_local):
         if self.exchange == "allgather":
@@ -400,7 +426,13 @@ class PartitionedSpMM:
             self._side.wait_stream(cur)
             with torch.cuda.stream(self._side):
                 full = self._exchange(blocks, B_local, pre)
-            self._mul_local(blocks, B_local, out)          # overlaps the all-gather
+            # pull mode: the local block starts when the rendezvous kernel has finished.  Launched before it, the
+            # local block fills every SM and the rendezvous (one small CTA that the pull waits for — the critical
+            # path at 8 GPUs) took 0.12-0.17 ms to get scheduled and to get its flag traffic through
+            # (profiles/r02_aq_timeline_n8.jsonl)
+            if self._after_barrier is not None and self._local_after_barrier(blocks, B_local):
+                cur.wait_event(self._after_barrier)
+            self._mul_local(blocks, B_local, out)          # overlaps the exchange
             cur.wait_stream(self._side)
             full.record_stream(cur)
         else:

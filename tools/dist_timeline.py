@@ -44,8 +44,11 @@ def step():
         ev["bar0"].record(part._side)
         part._rank_barrier()
         ev["bar1"].record(part._side)
+        after = torch.cuda.Event(); after.record(part._side)
         full = part._pull(blocks, ex, slot, k)
         ev["pull1"].record(part._side)
+    if part._local_after_barrier(blocks, B):
+        cur.wait_event(after)
     ev["loc0"].record(cur)
     part._mul_local(blocks, B, out)
     ev["loc1"].record(cur)
