@@ -395,6 +395,8 @@ static int launch_stream(const LaunchArgs& a, int64_t gs, unsigned ytiles) {
       case 7: launch_stream_cfg<TB, VEC, NV, 3, 12>(a, gs, ytiles); break;   // 40 regs, 48 warps/SM
       case 8: launch_stream_cfg<TB, VEC, NV, 3, 8>(a, gs, ytiles); break;
       case 9: launch_stream_cfg<TB, VEC, NV, 2, 16>(a, gs, ytiles); break;   // 32 regs, 64 warps/SM
+      case 10: launch_stream_cfg<TB, VEC, NV, 4, 9>(a, gs, ytiles); break;   // 56 regs, 36 warps/SM (no spills since the cp.async slab)
+      case 11: launch_stream_cfg<TB, VEC, NV, 8, 5>(a, gs, ytiles); break;   // 96 regs, 20 warps/SM, 8 in flight each
       default:
         if constexpr (R <= 2) launch_stream_cfg<TB, VEC, NV, 4, 10>(a, gs, ytiles);
         else launch_stream_cfg<TB, VEC, NV, 4, 8>(a, gs, ytiles);
