@@ -556,6 +556,7 @@ def run_single(args):
 
     with ClockSampler(0) as clk:
         ms_avg, ms_med, ms_min = time_steps(lambda: plan.spmm(B, out=C), args.steps, args.warmup, device)
+    step_list = list(time_steps.last)
     b_bytes = 4 if args.dtype == "f32" else 2
     abytes, flops = synth.spmm_bytes_flops(n, n, nnz, k, b_bytes=b_bytes)
     value = flops / (ms_avg * 1e-3) / 1e9
@@ -573,7 +574,7 @@ def run_single(args):
                    "l2": f"operands {abytes / 1e9:.2f} GB >> 126 MB L2; no flush needed",
                    "plan_build_s": round(plan_s, 2)},
         "gpu_launches": launches_per_step * args.steps,
-        "ms_median": ms_med, "ms_min": ms_min,
+        "ms_median": ms_med, "ms_min": ms_min, "ms_steps": step_list,
         "hbm_gbs_algorithmic": achieved, "pct_of_8TBs": 100 * achieved / 8000.0,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": None, "peak_source": peak_src,

@@ -395,11 +395,14 @@ static int launch_stream(const LaunchArgs& a, int64_t gs, unsigned ytiles) {
       case 7: launch_stream_cfg<TB, VEC, NV, 3, 12>(a, gs, ytiles); break;   // 40 regs, 48 warps/SM
       case 8: launch_stream_cfg<TB, VEC, NV, 3, 8>(a, gs, ytiles); break;
       case 9: launch_stream_cfg<TB, VEC, NV, 2, 16>(a, gs, ytiles); break;   // 32 regs, 64 warps/SM
-      case 10: launch_stream_cfg<TB, VEC, NV, 4, 9>(a, gs, ytiles); break;   // 56 regs, 36 warps/SM (no spills since the cp.async slab)
+      case 10: launch_stream_cfg<TB, VEC, NV, 4, 8>(a, gs, ytiles); break;   // 64 regs, 32 warps/SM (the default until r02_au)
       case 11: launch_stream_cfg<TB, VEC, NV, 8, 5>(a, gs, ytiles); break;   // 96 regs, 20 warps/SM, 8 in flight each
       default:
+        // fp32: ring 4 at 56 registers / 36 warps per SM since the (col,val) slab is a cp.async ring (no spills any
+        // more): products k=100 3.43 mean / 3.20 best against 3.47 / 3.33 at 64 registers / 32 warps
+        // (profiles/r02_au_stream_cfg.jsonl; both runs at the board's power cap)
         if constexpr (R <= 2) launch_stream_cfg<TB, VEC, NV, 4, 10>(a, gs, ytiles);
-        else launch_stream_cfg<TB, VEC, NV, 4, 8>(a, gs, ytiles);
+        else launch_stream_cfg<TB, VEC, NV, 4, 9>(a, gs, ytiles);
         break;
     }
   } else if constexpr (F <= 8) {
