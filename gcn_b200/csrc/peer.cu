@@ -31,35 +31,50 @@ struct PeerBases {
 // grid, 2.75 / 2.69 / 2.45 ms with 4 / 2 / 1 CTAs per SM, profiles/r01_n_*; default 1).
 // In flight: warps x kPullRowsPerWarp rows x row_bytes (148 x 8 x 4 x 400 B = 1.9 MB), about the
 // ~2 us x 900 GB/s the link needs.
+// (An L2 evict_first priority on the halo rows written here and on the peer loads changed nothing beside the local
+// block, profiles/r02_ax_timeline_n4.jsonl; the accesses are plain.)
+// Register budget: the kernel runs beside the local-block SpMM, whose occupancy is set by the register file.  At 80
+// registers x 256 threads the pull held 31 % of it and the local block lost a third of its warps (4 GPUs: 1.05 ms
+// beside the pull against 0.77 alone, profiles/r02_aw_timeline_n4.jsonl).  Hence: the peer bases are read from the
+// constant bank (__grid_constant__; a dynamically indexed by-value array would be copied to the stack), row indices
+// stay 32-bit until they are used, the vector loop is not unrolled (a 400-byte row is one trip), and the launch
+// bounds cap the kernel at 51 registers (13 k of the SM's 64 k: the fp32 SpMM keeps 7 of its 9 CTAs; 40 registers
+// would not give it an eighth and spill here).
 template <typename V>
-__global__ void __launch_bounds__(kPullWarps * 32)
-pull_rows_kernel(PeerBases bases, const int32_t* __restrict__ part, const int32_t* __restrict__ row,
-                 char* __restrict__ out, int64_t src_pitch, int64_t out_pitch, int64_t n_rows,
-                 int64_t first_row, int vecs_per_row) {
+__global__ void __launch_bounds__(kPullWarps * 32, 5)
+pull_rows_kernel(const __grid_constant__ PeerBases bases, const int32_t* __restrict__ part,
+                 const int32_t* __restrict__ row, char* __restrict__ out, int64_t src_pitch, int64_t out_pitch,
+                 int64_t n_rows, int64_t first_row, int vecs_per_row) {
   const int lane = threadIdx.x & 31;
   const int64_t n_warps = (int64_t)gridDim.x * kPullWarps;
+#pragma unroll 1
   for (int64_t w = (int64_t)blockIdx.x * kPullWarps + (threadIdx.x >> 5); w * kPullRowsPerWarp < n_rows;
        w += n_warps) {
     const int64_t r0 = w * kPullRowsPerWarp;
     const V* src[kPullRowsPerWarp];
-    V* dst[kPullRowsPerWarp];
+    int32_t rr[kPullRowsPerWarp];   // halo positions fit 32 bits (checked by gcnb_pull_rows)
 #pragma unroll
     for (int j = 0; j < kPullRowsPerWarp; ++j) {
       int64_t r = min(r0 + j, n_rows - 1);   // clamp: duplicates rewrite the same bytes
       r += first_row;                        // rotated start (see gcnb_pull_rows)
       if (r >= n_rows) r -= n_rows;
+      rr[j] = (int32_t)r;
       src[j] = reinterpret_cast<const V*>(bases.p[__ldg(part + r)] + (int64_t)__ldg(row + r) * src_pitch);
-      dst[j] = reinterpret_cast<V*>(out + r * out_pitch);
     }
+#pragma unroll 1
     for (int i = lane; i < vecs_per_row; i += 32) {
       V v[kPullRowsPerWarp];
 #pragma unroll
       for (int j = 0; j < kPullRowsPerWarp; ++j) v[j] = src[j][i];   // peer memory: plain (coherent) loads
 #pragma unroll
-      for (int j = 0; j < kPullRowsPerWarp; ++j) dst[j][i] = v[j];
+      for (int j = 0; j < kPullRowsPerWarp; ++j) *(reinterpret_cast<V*>(out + (int64_t)rr[j] * out_pitch) + i) = v[j];
     }
   }
 }
+
+}  // namespace gcnb
+
+namespace gcnb {
 
 // ---- the same pull through the TMA unit: no registers, no warps waiting on the link ---------------------
 // The LDG kernel above keeps warps x 4 rows in flight and holds them in registers (1.9 MB over the chip,
@@ -238,6 +253,7 @@ int gcnb_pull_rows(const void* const* bases, int n_parts, int64_t src_pitch_byte
                    int64_t n_rows, int64_t row_bytes, int64_t first_row, void* stream) {
   GCNB_REQUIRE(n_rows >= 0 && row_bytes >= 0, "negative size");
   GCNB_REQUIRE(first_row >= 0 && (first_row < n_rows || n_rows == 0), "first_row out of range");
+  GCNB_REQUIRE(n_rows < 0x7fffffffLL, "n_rows = %lld does not fit 32 bits", (long long)n_rows);
   if (n_rows == 0 || row_bytes == 0) return GCNB_OK;
   GCNB_REQUIRE(bases && part && row && out, "null pointer");
   GCNB_REQUIRE(n_parts >= 1 && n_parts <= kMaxParts, "n_parts = %d (1..%d)", n_parts, kMaxParts);

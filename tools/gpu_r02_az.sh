@@ -1,0 +1,11 @@
+#!/bin/bash
+# round 2, multi-GPU batch az: the lean pull kernel at 4 GPUs (timeline + bench line without epoch / e2e)
+tag=${1:-r02_az}; N=${2:-4}; o=gpurun_out; mkdir -p $o
+TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517"
+timeout 300 $TR tools/dist_timeline.py 2>>$o/${tag}_err.log | grep '^{' | tee -a $o/${tag}_timeline_n$N.jsonl | python -c "
+import sys, json
+for l in sys.stdin:
+    d = json.loads(l); print(d['rank'], 'step', round(d['step_ms'], 3), 'whole', round(d['whole_ms'], 3), 'bar', round(d['barrier_ms'], 3), 'pull', round(d['pull_ms'], 3), 'local', round(d['local_ms'], 3), 'remote', round(d['remote_ms'], 3), d['env'])"
+f=$o/${tag}_spmm_n${N}_pull_f32.json
+timeout 300 $TR bench.py --gpus $N --steps 20 --warmup 5 --no-cpu-baseline --no-e2e > $f 2> ${f%.json}.err
+echo "bench rc=$? $(grep -o '"ms_per_step": [0-9.]*\|"ms_median": [0-9.]*\|"max_rel_err": [0-9.e-]*\|"ms_per_epoch": [0-9.]*' $f | cut -c1-220 | paste -s -d' ')"
