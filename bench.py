@@ -945,6 +945,12 @@ def run_multi(args):
     if not args.no_epoch and args.workload in EPOCH_SHAPES:
         epoch = epoch_object_multi(args, part, n, device, barrier)
     halo_rows = int(blocks["halo_row"].numel()) if args.exchange == "pull" else (world - 1) * part.stride
+    # OUR kernels per step on this rank (NCCL's own kernels in all-gather mode are not counted): the two blocks'
+    # SpMM launches (+ their split-row reductions), in pull mode the halo pull and, between GPUs, the rendezvous kernel
+    launches_per_step = (kernel_launches_per_spmm(blocks["local"].info(), k, "f32")
+                         + kernel_launches_per_spmm(blocks["remote"].info(), k, args.wire))
+    if args.exchange == "pull":
+        launches_per_step += 1 + (1 if getattr(part, "_peer_flags", None) is not None else 0)
     t = torch.tensor([ms_avg, ms_med, ms_min, ph_local, ph_exch, ph_remote, halo_rows, e2e_ms], device=device,
                      dtype=torch.float64)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -976,7 +982,7 @@ def run_multi(args):
             "ms_steps_rank0": step_list,
             "phase_ms_alone": {"local_block_spmm": ph_local, "exchange": ph_exch, "remote_block_spmm": ph_remote,
                                "note": "median of 5, each phase run alone, max over ranks; the step overlaps the first two"},
-            "gpu_launches": (3 if args.exchange == "pull" else 2) * args.steps, "ms_median": ms_med, "ms_min": ms_min,
+            "gpu_launches": launches_per_step * args.steps, "ms_median": ms_med, "ms_min": ms_min,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak * world, "unit": "GB/s",
                          "frac": achieved / (peak * world), "traffic": None, "peak_source": peak_src,
                          "note": "aggregate: algorithmic bytes of the whole SpMM over N x per-GPU HBM peak; "
