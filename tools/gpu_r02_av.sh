@@ -1,7 +1,7 @@
 #!/bin/bash
 # round 2, GPU batch av: after making 36 warps/SM the fp32 stream default — SpMM / layer / dist suites, default bench line
 tag=${1:-r02_av}; o=gpurun_out; mkdir -p $o
-timeout 900 python -m pytest tests/test_spmm_gpu.py tests/test_layers_gpu.py tests/test_dist_gpu.py tests/test_zz_no_alloc.py -m gpu -x -q > $o/${tag}_pytest.log 2>&1; echo "pytest exit $?" >> $o/${tag}_pytest.log; tail -n 2 $o/${tag}_pytest.log
+timeout 900 python -m pytest tests/test_spmm_gpu.py tests/test_layers_gpu.py tests/test_dist_gpu.py tests/test_zzz_no_alloc.py -m gpu -x -q > $o/${tag}_pytest.log 2>&1; echo "pytest exit $?" >> $o/${tag}_pytest.log; tail -n 2 $o/${tag}_pytest.log
 timeout 900 python bench.py > $o/${tag}_bench_default.json 2> $o/${tag}_bench_default.err; echo "bench rc=$?"
 python - <<PY
 import json
